@@ -1,0 +1,126 @@
+/*
+ * pntf_b200.h -- C-ABI of the B200-native P-NTFields hot path (libpntf_b200.so).
+ *
+ * The reference (yhsong0804/P-NTFields) is pure Python/PyTorch and has no FFI; its boundary for this
+ * path is the Python class API of models/model_res_sigmoid.py (S:) and
+ * models/model_res_sigmoid_multi.py (M:).  Each entry point below states which reference method(s)
+ * it replaces.  The Python mirror of those classes lives in p-ntfields_b200/pntf and calls these
+ * symbols through ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer into caller-owned memory (fp32, row-major, contiguous)
+ *     unless its name starts with h_; the library never allocates, frees or keeps pointers;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, no host sync
+ *     (except pntf_plan when h_sync != 0);
+ *   - return value 0 = ok, nonzero = error (PNTF_ERR_*); pntf_last_error() returns a
+ *     thread-local message;
+ *   - d = C-space dimension (3 or 6), a start/goal pair is 2d floats (x0 then x1);
+ *   - params = the flat fp32 parameter buffer in state_dict order of S:159-181 / M:153-175
+ *     (576129 floats; see pntf_param_offset);
+ *   - B = Fourier matrix [E, d, 128] (one per environment; single-env callers pass E = 1 and
+ *     NN.B which is already [d,128], S:139).  Pair n of coords[E*N, 2d] uses B[n / N];
+ *   - prec: PNTF_PREC_FP32 = fp32 SIMT verify mode, PNTF_PREC_TC = tcgen05 tensor-core mode.
+ */
+#ifndef PNTF_B200_H_
+#define PNTF_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PNTF_PARAM_COUNT 576129
+#define PNTF_NUM_TENSORS 30
+
+enum { PNTF_OK = 0, PNTF_ERR_ARG = 1, PNTF_ERR_UNSUPPORTED = 2, PNTF_ERR_WORKSPACE = 3, PNTF_ERR_CUDA = 4 };
+enum { PNTF_PREC_FP32 = 0, PNTF_PREC_TC = 1 };
+/* derivative order of the forward pass: NN.out / NN.out_grad / NN.out_laplace */
+enum { PNTF_MODE_VALUE = 0, PNTF_MODE_GRAD = 1, PNTF_MODE_LAPLACE = 2 };
+/* Model.Loss flavour: S:869-936 (square roots on the ratio) / M:897-951 (none, + 0.01|B|^2) */
+enum { PNTF_LOSS_SINGLE = 0, PNTF_LOSS_MULTI = 1 };
+/* pntf_field kinds */
+enum {
+  PNTF_FIELD_TRAVEL_TIME = 0, /* Model.TravelTimes  S:1169-1183, M:1173-1186 */
+  PNTF_FIELD_SPEED = 1,       /* Model.Speed        S:1192-1216, M:1195-1216 */
+  PNTF_FIELD_SPEED2 = 2,      /* Model.Speed2       S:1218-1245 (uses gamma)  */
+  PNTF_FIELD_DIRECTION = 3    /* Model.Gradient     S:1247-1282, M:1218-1248 (row-wise), out [N,2d] */
+};
+/* gradient flavour for PNTF_FIELD_DIRECTION / pntf_plan / MODE_GRAD:
+ * EXACT = true grad tau (S: autograd, NN.out_grad); COMPAT = what M:402-647 (out_backgrad) returns,
+ * whose first encoder gate is evaluated at softplus(y) (M:435-438). */
+enum { PNTF_GRAD_EXACT = 0, PNTF_GRAD_COMPAT = 1 };
+/* workspace queries */
+enum { PNTF_OP_FORWARD = 0, PNTF_OP_LOSS_FWD = 1, PNTF_OP_LOSS_BWD = 2, PNTF_OP_PLAN = 3, PNTF_OP_FIELD = 4 };
+
+int pntf_version(void);
+const char* pntf_last_error(void);
+
+/* Offset / shape of tensor `index` (0..29, state_dict order: encoder.0.weight, encoder.0.bias, ...)
+ * inside the flat parameter buffer.  Returns 0, or PNTF_ERR_ARG for a bad index. */
+int pntf_param_offset(int index, int64_t* offset, int64_t* rows, int64_t* cols, int* used_by_forward);
+
+/* Bytes of scratch the op needs for this shape (pass the same buffer as `workspace`).  For
+ * PNTF_OP_LOSS_BWD `budget_bytes` (0 = default 8 GiB) caps the activation stash; larger batches are
+ * processed in chunks inside one call. */
+size_t pntf_workspace_bytes(int op, int E, int64_t N, int d, int prec, size_t budget_bytes);
+
+/* NN.out / NN.out_grad / NN.out_laplace (S:212-256, 513-613, 676-820; M:215-259, 303-400, 710-848).
+ * tau[E*N], dtau[E*N,2d] (mode>=GRAD), ltau[E*N,2d] (mode LAPLACE); unused outputs may be NULL. */
+int pntf_forward(int mode, int grad_flavour, const float* params, const float* B, const float* coords,
+                 int E, int64_t N, int d, float* tau, float* dtau, float* ltau, int prec,
+                 void* workspace, size_t workspace_bytes, void* stream);
+
+/* Model.TravelTimes / Speed / Speed2 / Gradient: out[E*N] (DIRECTION: out[E*N,2d]). */
+int pntf_field(int kind, int grad_flavour, const float* params, const float* B, const float* coords,
+               int E, int64_t N, int d, float gamma, float* out, int prec,
+               void* workspace, size_t workspace_bytes, void* stream);
+
+/* Model.Loss forward only (S:869-936, M:897-951).  speed[E*N,2] is used as alpha*speed+1-alpha
+ * (the trainer's interpolation, S:1063 / M:1051; pass alpha = 1 for the raw Loss()).
+ * diff[E*N] = per-pair residual; loss_out[2] = {loss = beta*loss_n, loss_n} (device). */
+int pntf_loss_fwd(int variant, const float* params, const float* B, const float* coords, const float* speed,
+                  int E, int64_t N, int d, float alpha, float beta, float gamma,
+                  float* diff, float* loss_out, int prec,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
+/* Model.Loss + loss.backward() (S:1065-1071, M:1070-1076): same outputs as pntf_loss_fwd, and
+ * grad_params[PNTF_PARAM_COUNT] += d loss / d params (the caller zeroes it; encoder1.0.* is never
+ * written -- the reference leaves its .grad None). */
+int pntf_loss_bwd(int variant, const float* params, const float* B, const float* coords, const float* speed,
+                  int E, int64_t N, int d, float alpha, float beta, float gamma,
+                  float* diff, float* loss_out, float* grad_params, int prec,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
+/* torch.optim.AdamW step on flat buffers (S:954-956,1074; M:960-962,1079): decoupled weight decay,
+ * bias-corrected; elements whose mask byte is 0 are left untouched (parameters with grad None).
+ * grad_scale multiplies the gradient first (1/world_size after an all-reduce(sum)). */
+int pntf_adamw(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, const uint8_t* mask,
+               int64_t n, float lr, float beta1, float beta2, float eps, float weight_decay,
+               int64_t step, float grad_scale, void* stream);
+
+/* Batched bidirectional path integration (test/gib_plan.py:53-86, test/arm_plan.py:111-152):
+ * per query, while |x1-x0| > thr: XP += eta*Gradient(XP), at most max_iter+1 steps.
+ * waypoints[Q, max_iter+2, 2d]: row 0 = the query, row k = position after step k, rows after the
+ * last step repeat the final position; nsteps[Q] = steps taken. */
+int pntf_plan(const float* params, const float* B, const float* start_goal, int64_t Q, int d,
+              float eta, float thr, int max_iter, int grad_flavour,
+              float* waypoints, int32_t* nsteps, int prec,
+              void* workspace, size_t workspace_bytes, void* stream);
+
+/* Measurement aid for bench.py: between begin and end every kernel (group) the library launches is
+ * bracketed by CUDA events on its stream; end synchronises on them and returns, per kernel class
+ * (0 pack, 1 forward, 2 reverse, 3 dW, 4 loss-finalize, 5 adamw, 6 plan, 7 tc-forward, 8 tc-reverse,
+ * 9 tc-dW), the summed device time in ms and the number of bracketed launches (groups). */
+#define PNTF_KERNEL_CLASSES 10
+int pntf_profile_begin(void);
+int pntf_profile_end(double* ms_by_class, int64_t* count_by_class, int n_classes);
+
+/* number of kernels the library has launched since load (for bench.py's gpu_launches) */
+int64_t pntf_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PNTF_B200_H_ */

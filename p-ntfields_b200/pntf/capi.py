@@ -1,0 +1,193 @@
+"""ctypes binding of libpntf_b200.so (C-ABI: include/pntf_b200.h).
+
+Every wrapper takes torch CUDA tensors, checks dtype/contiguity/device, passes raw device pointers
+and the current torch CUDA stream, and raises RuntimeError on a nonzero status.
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpntf_b200.so")
+
+PARAM_COUNT = 576129
+PREC_FP32, PREC_TC = 0, 1
+MODE_VALUE, MODE_GRAD, MODE_LAPLACE = 0, 1, 2
+LOSS_SINGLE, LOSS_MULTI = 0, 1
+FIELD_TRAVEL_TIME, FIELD_SPEED, FIELD_SPEED2, FIELD_DIRECTION = 0, 1, 2, 3
+GRAD_EXACT, GRAD_COMPAT = 0, 1
+OP_FORWARD, OP_LOSS_FWD, OP_LOSS_BWD, OP_PLAN, OP_FIELD = 0, 1, 2, 3, 4
+
+EXPORTS = ["pntf_version", "pntf_last_error", "pntf_param_offset", "pntf_workspace_bytes", "pntf_forward",
+           "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_adamw", "pntf_plan", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end"]
+
+_lib = None
+
+
+def lib():
+    """Load the shared library (built by p-ntfields_b200/build.py / __graft_entry__.build())."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError("libpntf_b200.so is missing (%s): run `python p-ntfields_b200/build.py`; "
+                           "there is no CPU fallback" % LIB_PATH)
+    L = ctypes.CDLL(LIB_PATH)
+    c_i, c_i64, c_f, c_p, c_sz = ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_void_p, ctypes.c_size_t
+    L.pntf_version.restype = c_i
+    L.pntf_last_error.restype = ctypes.c_char_p
+    L.pntf_launch_count.restype = c_i64
+    L.pntf_param_offset.argtypes = [c_i, ctypes.POINTER(c_i64), ctypes.POINTER(c_i64), ctypes.POINTER(c_i64),
+                                    ctypes.POINTER(c_i)]
+    L.pntf_workspace_bytes.restype = c_sz
+    L.pntf_workspace_bytes.argtypes = [c_i, c_i, c_i64, c_i, c_i, c_sz]
+    L.pntf_forward.argtypes = [c_i, c_i, c_p, c_p, c_p, c_i, c_i64, c_i, c_p, c_p, c_p, c_i, c_p, c_sz, c_p]
+    L.pntf_field.argtypes = [c_i, c_i, c_p, c_p, c_p, c_i, c_i64, c_i, c_f, c_p, c_i, c_p, c_sz, c_p]
+    L.pntf_loss_fwd.argtypes = [c_i, c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_f, c_f, c_f, c_p, c_p, c_i, c_p, c_sz, c_p]
+    L.pntf_loss_bwd.argtypes = [c_i, c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_f, c_f, c_f, c_p, c_p, c_p, c_i, c_p,
+                                c_sz, c_p]
+    L.pntf_adamw.argtypes = [c_p, c_p, c_p, c_p, c_p, c_i64, c_f, c_f, c_f, c_f, c_f, c_i64, c_f, c_p]
+    L.pntf_plan.argtypes = [c_p, c_p, c_p, c_i64, c_i, c_f, c_f, c_i, c_i, c_p, c_p, c_i, c_p, c_sz, c_p]
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise RuntimeError("libpntf_b200: error %d: %s" % (rc, lib().pntf_last_error().decode()))
+
+
+def _ptr(t, dtype=torch.float32, name="tensor"):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("%s must be a CUDA tensor (no CPU fallback)" % name)
+    if t.dtype != dtype or not t.is_contiguous():
+        raise RuntimeError("%s must be contiguous %s" % (name, dtype))
+    return t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+_ws_cache = {}
+
+
+def workspace(nbytes, device):
+    """A cached scratch buffer of at least nbytes on `device` (grown geometrically)."""
+    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = None
+        _ws_cache.pop(key, None)
+        buf = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    return buf
+
+
+def workspace_bytes(op, E, N, d, prec=PREC_FP32, budget=0):
+    n = lib().pntf_workspace_bytes(op, E, N, d, prec, budget)
+    if n == 0:
+        raise RuntimeError("libpntf_b200: unsupported configuration (d=%d, prec=%d)" % (d, prec))
+    return n
+
+
+def launch_count():
+    return int(lib().pntf_launch_count())
+
+
+KERNEL_CLASSES = ("pack", "forward", "reverse", "dw", "finalize", "adamw", "plan", "tc_forward", "tc_reverse", "tc_dw")
+
+
+def profile_begin():
+    _check(lib().pntf_profile_begin())
+
+
+def profile_end():
+    """{class: (ms, launches)} of everything launched since profile_begin()."""
+    n = len(KERNEL_CLASSES)
+    ms = (ctypes.c_double * n)()
+    cnt = (ctypes.c_int64 * n)()
+    _check(lib().pntf_profile_end(ms, cnt, n))
+    return {KERNEL_CLASSES[i]: (ms[i], cnt[i]) for i in range(n)}
+
+
+def param_table():
+    """[(offset, rows, cols, used)] for the 30 state_dict tensors."""
+    out = []
+    o, r, c, u = ctypes.c_int64(), ctypes.c_int64(), ctypes.c_int64(), ctypes.c_int()
+    for i in range(30):
+        _check(lib().pntf_param_offset(i, ctypes.byref(o), ctypes.byref(r), ctypes.byref(c), ctypes.byref(u)))
+        out.append((o.value, r.value, c.value, u.value))
+    return out
+
+
+def forward(mode, params, B, coords, E, N, d, prec=PREC_FP32, grad_flavour=GRAD_EXACT):
+    """tau[E*N], dtau[E*N,2d] or None, ltau[E*N,2d] or None."""
+    dev = coords.device
+    n = E * N
+    tau = torch.empty(n, dtype=torch.float32, device=dev)
+    dtau = torch.empty(n, 2 * d, dtype=torch.float32, device=dev) if mode >= MODE_GRAD else None
+    ltau = torch.empty(n, 2 * d, dtype=torch.float32, device=dev) if mode >= MODE_LAPLACE else None
+    ws = workspace(workspace_bytes(OP_FORWARD, E, N, d, prec), dev)
+    _check(lib().pntf_forward(mode, grad_flavour, _ptr(params, name="params"), _ptr(B, name="B"),
+                              _ptr(coords, name="coords"), E, N, d, _ptr(tau), _ptr(dtau), _ptr(ltau), prec,
+                              ws.data_ptr(), ws.numel(), _stream()))
+    return tau, dtau, ltau
+
+
+def field(kind, params, B, coords, E, N, d, gamma=0.0, prec=PREC_FP32, grad_flavour=GRAD_EXACT):
+    dev = coords.device
+    n = E * N
+    shape = (n, 2 * d) if kind == FIELD_DIRECTION else (n,)
+    out = torch.empty(shape, dtype=torch.float32, device=dev)
+    ws = workspace(workspace_bytes(OP_FIELD, E, N, d, prec), dev)
+    _check(lib().pntf_field(kind, grad_flavour, _ptr(params, name="params"), _ptr(B, name="B"),
+                            _ptr(coords, name="coords"), E, N, d, float(gamma), _ptr(out), prec, ws.data_ptr(),
+                            ws.numel(), _stream()))
+    return out
+
+
+def loss(variant, params, B, coords, speed, E, N, d, alpha, beta, gamma, grad_out=None, prec=PREC_FP32,
+         budget=0, diff=None, loss_out=None):
+    """Returns (loss_out[2] device tensor, diff[E*N]); accumulates into grad_out when given."""
+    dev = coords.device
+    n = E * N
+    if diff is None:
+        diff = torch.empty(n, dtype=torch.float32, device=dev)
+    if loss_out is None:
+        loss_out = torch.empty(2, dtype=torch.float32, device=dev)
+    common = (variant, _ptr(params, name="params"), _ptr(B, name="B"), _ptr(coords, name="coords"),
+              _ptr(speed, name="speed"), E, N, d, float(alpha), float(beta), float(gamma), _ptr(diff), _ptr(loss_out))
+    if grad_out is None:
+        ws = workspace(workspace_bytes(OP_LOSS_FWD, E, N, d, prec), dev)
+        _check(lib().pntf_loss_fwd(*common, prec, ws.data_ptr(), ws.numel(), _stream()))
+    else:
+        if grad_out.numel() != PARAM_COUNT:
+            raise RuntimeError("grad_out must have %d elements" % PARAM_COUNT)
+        ws = workspace(workspace_bytes(OP_LOSS_BWD, E, N, d, prec, budget), dev)
+        _check(lib().pntf_loss_bwd(*common, _ptr(grad_out, name="grad_out"), prec, ws.data_ptr(), ws.numel(),
+                                   _stream()))
+    return loss_out, diff
+
+
+def adamw(params, grads, exp_avg, exp_avg_sq, mask, step, lr=1e-3, betas=(0.9, 0.999), eps=1e-8,
+          weight_decay=0.1, grad_scale=1.0):
+    n = params.numel()
+    _check(lib().pntf_adamw(_ptr(params, name="params"), _ptr(grads, name="grads"), _ptr(exp_avg), _ptr(exp_avg_sq),
+                            _ptr(mask, torch.uint8, "mask"), n, float(lr), float(betas[0]), float(betas[1]),
+                            float(eps), float(weight_decay), int(step), float(grad_scale), _stream()))
+
+
+def plan(params, B, start_goal, d, eta, thr, max_iter, grad_flavour=GRAD_EXACT, prec=PREC_FP32):
+    dev = start_goal.device
+    Q = start_goal.shape[0]
+    way = torch.empty(Q, max_iter + 2, 2 * d, dtype=torch.float32, device=dev)
+    nsteps = torch.zeros(Q, dtype=torch.int32, device=dev)
+    ws = workspace(workspace_bytes(OP_PLAN, 1, Q, d, prec), dev)
+    _check(lib().pntf_plan(_ptr(params, name="params"), _ptr(B, name="B"), _ptr(start_goal, name="start_goal"), Q, d,
+                           float(eta), float(thr), int(max_iter), grad_flavour, _ptr(way),
+                           _ptr(nsteps, torch.int32), prec, ws.data_ptr(), ws.numel(), _stream()))
+    return way, nsteps
