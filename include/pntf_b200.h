@@ -95,10 +95,12 @@ int pntf_loss_bwd(int variant, const float* params, const float* B, const float*
 
 /* torch.optim.AdamW step on flat buffers (S:954-956,1074; M:960-962,1079): decoupled weight decay,
  * bias-corrected; elements whose mask byte is 0 are left untouched (parameters with grad None).
- * grad_scale multiplies the gradient first (1/world_size after an all-reduce(sum)). */
+ * grad_scale multiplies the gradient first (1/world_size after an all-reduce(sum)).  Hyper-parameters
+ * are doubles (Python floats): the derived constants 1-beta, lr/(1-beta1^t), ... are formed in double
+ * exactly as torch does before they are rounded to fp32. */
 int pntf_adamw(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, const uint8_t* mask,
-               int64_t n, float lr, float beta1, float beta2, float eps, float weight_decay,
-               int64_t step, float grad_scale, void* stream);
+               int64_t n, double lr, double beta1, double beta2, double eps, double weight_decay,
+               int64_t step, double grad_scale, void* stream);
 
 /* Batched bidirectional path integration (test/gib_plan.py:53-86, test/arm_plan.py:111-152):
  * per query, while |x1-x0| > thr: XP += eta*Gradient(XP), at most max_iter+1 steps.

@@ -362,17 +362,17 @@ int pntf_loss_bwd(int variant, const float* params, const float* B, const float*
 }
 
 int pntf_adamw(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, const uint8_t* mask, int64_t n,
-               float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
-               void* stream) {
+               double lr, double beta1, double beta2, double eps, double weight_decay, int64_t step,
+               double grad_scale, void* stream) {
   if (!params || !grads || !exp_avg || !exp_avg_sq || n < 0 || step < 1) return fail(PNTF_ERR_ARG, "bad adamw argument");
   if (n == 0) return PNTF_OK;
   AdamArgs a{};
   a.p = params; a.g = grads; a.m = exp_avg; a.v = exp_avg_sq; a.mask = mask; a.n = n;
-  a.decay = float(1.0 - double(lr) * double(weight_decay));
-  a.b1 = beta1; a.b2 = beta2; a.eps = eps;
-  a.step_size = float(double(lr) / (1.0 - std::pow(double(beta1), double(step))));
-  a.bc2_sqrt = float(std::sqrt(1.0 - std::pow(double(beta2), double(step))));
-  a.grad_scale = grad_scale;
+  a.decay = float(1.0 - lr * weight_decay);
+  a.omb1 = float(1.0 - beta1); a.b2 = float(beta2); a.omb2 = float(1.0 - beta2); a.eps = float(eps);
+  a.step_size = float(lr / (1.0 - std::pow(beta1, double(step))));
+  a.bc2_sqrt = float(std::sqrt(1.0 - std::pow(beta2, double(step))));
+  a.grad_scale = float(grad_scale);
   const int blocks = int((n + 255) / 256 < 4 * sm_count() ? (n + 255) / 256 : 4 * sm_count());
   prof_start(KC_ADAMW, static_cast<cudaStream_t>(stream));
   adamw_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);

@@ -23,6 +23,7 @@ struct Cfg {
   static constexpr int G = kThreads / P;            // feature groups (threads per point)
   static constexpr int NE = ORDER * D, CE = 1 + NE; // derivative / total columns per endpoint
   static constexpr int NG = 2 * NE, CG = 1 + NG;    // ... per pair in the generator
+  static constexpr int N1 = (ORDER >= 1) ? 2 * D : 0;  // first-derivative columns per pair (= size of dtau / ltau rows)
   static constexpr int RE = P * CE, RSE = RE | 1;   // rows per encoder pass, odd smem row stride
   static constexpr int RG = P * CG, RSG = RG | 1;
   static constexpr int BUF = 256 * RSG;             // one generator activation buffer (floats)

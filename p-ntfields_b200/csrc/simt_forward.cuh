@@ -220,10 +220,10 @@ __device__ __forceinline__ void output_rules(const float* y, float& tau, float* 
   tau = o.o;
   if constexpr (C::ORDER >= 1) {
 #pragma unroll
-    for (int i = 0; i < C::NG; ++i) {
+    for (int i = 0; i < C::N1; ++i) {
       const float dy = y[1 + i];
       dtau[i] = dy * o.o1;
-      if constexpr (C::ORDER >= 2) ltau[i] = fmaf(dy * dy, o.o2, y[1 + C::NG + i] * o.o1);
+      if constexpr (C::ORDER >= 2) ltau[i] = fmaf(dy * dy, o.o2, y[1 + C::N1 + i] * o.o1);
     }
   }
 }
@@ -243,16 +243,16 @@ __global__ void __launch_bounds__(kThreads, 1) simt_forward_kernel(const FwdArgs
     if (threadIdx.x < C::P) {
       const int64_t pair = pair0 + threadIdx.x;
       if (ts.valid[threadIdx.x]) {
-        float tau, dtau[C::NG > 0 ? C::NG : 1], ltau[C::NG > 0 ? C::NG : 1];
+        float tau, dtau[C::N1 > 0 ? C::N1 : 1], ltau[C::N1 > 0 ? C::N1 : 1];
         output_rules<C>(y13s + threadIdx.x * C::CG, tau, dtau, ltau);
         if (a.tau) a.tau[pair] = tau;
         if constexpr (ORDER >= 1) {
           if (a.dtau)
-            for (int i = 0; i < C::NG; ++i) a.dtau[pair * C::NG + i] = dtau[i];
+            for (int i = 0; i < C::N1; ++i) a.dtau[pair * C::N1 + i] = dtau[i];
         }
         if constexpr (ORDER >= 2) {
           if (a.ltau)
-            for (int i = 0; i < C::NG; ++i) a.ltau[pair * C::NG + i] = ltau[i];
+            for (int i = 0; i < C::N1; ++i) a.ltau[pair * C::N1 + i] = ltau[i];
         }
         const float* x = ts.x[threadIdx.x];
         if constexpr (TAIL == TAIL_LOSS && ORDER == 2) {

@@ -34,7 +34,7 @@ __global__ void pack_weights_kernel(const float* __restrict__ params, float* __r
 struct AdamArgs {
   float* p; const float* g; float* m; float* v; const uint8_t* mask; int64_t n;
   float decay;        // 1 - lr*wd
-  float b1, b2, eps;
+  float omb1, b2, omb2, eps;   // 1-beta1, beta2, 1-beta2 (rounded from double like torch's scalars)
   float step_size;    // lr / (1 - b1^t)
   float bc2_sqrt;     // sqrt(1 - b2^t)
   float grad_scale;
@@ -47,8 +47,8 @@ __global__ void adamw_kernel(const AdamArgs a) {
     float p = a.p[i] * a.decay;
     float m = a.m[i];
     float v = a.v[i];
-    m = m + (g - m) * (1.0f - a.b1);
-    v = v * a.b2 + (1.0f - a.b2) * g * g;
+    m = m + (g - m) * a.omb1;
+    v = fmaf(a.omb2 * g, g, v * a.b2);
     const float denom = sqrtf(v) / a.bc2_sqrt + a.eps;
     p = p - a.step_size * (m / denom);
     a.p[i] = p; a.m[i] = m; a.v[i] = v;
@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(kThreads, 1) simt_plan_kernel(const PlanArgs p
       forward_tile<C, false>(a, ts, arena, y13s, pair0);
       if (threadIdx.x < P && active[threadIdx.x]) {
         const int p = threadIdx.x;
-        float tau, dtau[C::NG], ltau[1];
+        float tau, dtau[C::N1], ltau[1];
         output_rules<C>(y13s + p * C::CG, tau, dtau, ltau);
         float dir[2 * D];
         field_direction<D>(ts.x[p], tau, dtau, dir);

@@ -65,7 +65,7 @@ __device__ __forceinline__ void combine_bwd(const float* Gb, const float* __rest
 template <int D>
 __global__ void __launch_bounds__(kThreads, 1) simt_reverse_kernel(const BwdArgs b) {
   using C = Cfg<D, 2>;
-  constexpr int P = C::P, CE = C::CE, CG = C::CG, RSE = C::RSE, RSG = C::RSG, NG = C::NG;
+  constexpr int P = C::P, CE = C::CE, CG = C::CG, RSE = C::RSE, RSG = C::RSG, NG = C::N1;
   extern __shared__ __align__(16) float arena[];
   __shared__ float g13s[C::RG];
   __shared__ TileState<D, P> ts;

@@ -47,7 +47,8 @@ def lib():
     L.pntf_loss_fwd.argtypes = [c_i, c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_f, c_f, c_f, c_p, c_p, c_i, c_p, c_sz, c_p]
     L.pntf_loss_bwd.argtypes = [c_i, c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_f, c_f, c_f, c_p, c_p, c_p, c_i, c_p,
                                 c_sz, c_p]
-    L.pntf_adamw.argtypes = [c_p, c_p, c_p, c_p, c_p, c_i64, c_f, c_f, c_f, c_f, c_f, c_i64, c_f, c_p]
+    c_d = ctypes.c_double
+    L.pntf_adamw.argtypes = [c_p, c_p, c_p, c_p, c_p, c_i64, c_d, c_d, c_d, c_d, c_d, c_i64, c_d, c_p]
     L.pntf_plan.argtypes = [c_p, c_p, c_p, c_i64, c_i, c_f, c_f, c_i, c_i, c_p, c_p, c_i, c_p, c_sz, c_p]
     _lib = L
     return L
