@@ -119,6 +119,11 @@ int pntf_plan(const float* params, const float* B, const float* start_goal, int6
 int pntf_profile_begin(void);
 int pntf_profile_end(double* ms_by_class, int64_t* count_by_class, int n_classes);
 
+/* Diagnostic of the tcgen05 plumbing (operand layouts, descriptors, TMEM mapping); no reference
+ * counterpart.  W, X, C: [128,128] fp32 device arrays; out[3,128,128] = {W X, C + W X, X X^T} computed
+ * with fp16 operands and fp32 accumulation on the tensor cores. */
+int pntf_tc_selftest(const float* W, const float* X, const float* C, float* out, void* stream);
+
 /* number of kernels the library has launched since load (for bench.py's gpu_launches) */
 int64_t pntf_launch_count(void);
 

@@ -20,7 +20,8 @@ GRAD_EXACT, GRAD_COMPAT = 0, 1
 OP_FORWARD, OP_LOSS_FWD, OP_LOSS_BWD, OP_PLAN, OP_FIELD = 0, 1, 2, 3, 4
 
 EXPORTS = ["pntf_version", "pntf_last_error", "pntf_param_offset", "pntf_workspace_bytes", "pntf_forward",
-           "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_adamw", "pntf_plan", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end"]
+           "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_adamw", "pntf_plan", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end",
+           "pntf_tc_selftest"]
 
 _lib = None
 
@@ -50,6 +51,7 @@ def lib():
     c_d = ctypes.c_double
     L.pntf_adamw.argtypes = [c_p, c_p, c_p, c_p, c_p, c_i64, c_d, c_d, c_d, c_d, c_d, c_i64, c_d, c_p]
     L.pntf_plan.argtypes = [c_p, c_p, c_p, c_i64, c_i, c_f, c_f, c_i, c_i, c_p, c_p, c_i, c_p, c_sz, c_p]
+    L.pntf_tc_selftest.argtypes = [c_p, c_p, c_p, c_p, c_p]
     _lib = L
     return L
 
@@ -192,3 +194,10 @@ def plan(params, B, start_goal, d, eta, thr, max_iter, grad_flavour=GRAD_EXACT, 
                            float(eta), float(thr), int(max_iter), grad_flavour, _ptr(way),
                            _ptr(nsteps, torch.int32), prec, ws.data_ptr(), ws.numel(), _stream()))
     return way, nsteps
+
+
+def tc_selftest(W, X, C):
+    """out[3,128,128] = {W X, C + W X, X X^T} on the tensor cores (fp16 operands, fp32 accumulate)."""
+    out = torch.empty(3, 128, 128, dtype=torch.float32, device=W.device)
+    _check(lib().pntf_tc_selftest(_ptr(W), _ptr(X), _ptr(C), _ptr(out), _stream()))
+    return out

@@ -298,3 +298,17 @@ def test_training_loop_reduces_loss(capi):
     assert len(hist) == 6
     assert all(np.isfinite(h[1]) for h in hist)
     assert hist[-1][1] < hist[0][1]
+
+
+def test_tc_selftest_plumbing(capi):
+    """tcgen05 operand layouts / descriptors / TMEM mapping against numpy (fp16-rounded operands)."""
+    rs = np.random.RandomState(5)
+    W = rs.normal(size=(128, 128)).astype(np.float32)
+    X = rs.normal(size=(128, 128)).astype(np.float32)
+    C = rs.normal(size=(128, 128)).astype(np.float32)
+    out = capi.tc_selftest(cu(W), cu(X), cu(C)).cpu().numpy()
+    Wh = W.astype(np.float16).astype(np.float64)
+    Xh = X.astype(np.float16).astype(np.float64)
+    assert np.abs(out[0] - Wh @ Xh).max() < 2e-4
+    assert np.abs(out[1] - (C + Wh @ Xh)).max() < 2e-4
+    assert np.abs(out[2] - Xh @ Xh.T).max() < 2e-4
