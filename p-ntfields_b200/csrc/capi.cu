@@ -16,7 +16,7 @@ namespace pntf {
 static thread_local char g_err[512] = "";
 static std::atomic<int64_t> g_launches{0};
 
-static int fail(int code, const char* fmt, ...) {
+int fail(int code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
@@ -31,8 +31,6 @@ static int fail(int code, const char* fmt, ...) {
   } while (0)
 
 // ---- optional per-kernel-class timing with CUDA events on the launching stream (bench.py) ----
-enum { KC_PACK = 0, KC_FORWARD, KC_REVERSE, KC_DW, KC_FINALIZE, KC_ADAMW, KC_PLAN, KC_TC_FORWARD, KC_TC_REVERSE,
-       KC_TC_DW, KC_COUNT };
 struct ProfRec { int cls; cudaEvent_t a, b; };
 constexpr int kProfMax = 8192;
 static bool g_prof_on = false;
@@ -40,7 +38,7 @@ static int g_prof_n = 0;
 static ProfRec g_prof[kProfMax];
 static int g_prof_created = 0;
 
-static void prof_start(int cls, cudaStream_t s) {
+void prof_start(int cls, cudaStream_t s) {
   if (!g_prof_on || g_prof_n >= kProfMax) return;
   ProfRec& r = g_prof[g_prof_n];
   if (g_prof_n >= g_prof_created) {
@@ -51,20 +49,20 @@ static void prof_start(int cls, cudaStream_t s) {
   r.cls = cls;
   cudaEventRecord(r.a, s);
 }
-static void prof_stop(cudaStream_t s) {
+void prof_stop(cudaStream_t s) {
   if (!g_prof_on || g_prof_n >= kProfMax) return;
   cudaEventRecord(g_prof[g_prof_n].b, s);
   ++g_prof_n;
 }
 
-static int launch_check(const char* what) {
+int launch_check(const char* what) {
   g_launches.fetch_add(1, std::memory_order_relaxed);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(PNTF_ERR_CUDA, "launch %s: %s", what, cudaGetErrorString(e));
   return PNTF_OK;
 }
 
-static int sm_count() {
+int sm_count() {
   static int n = 0;
   if (n == 0) {
     int dev = 0;
@@ -313,13 +311,17 @@ int pntf_field(int kind, int grad_flavour, const float* params, const float* B, 
                         nullptr, nullptr, nullptr, out, nullptr, workspace, workspace_bytes, stream);
 }
 
-static int finalize_loss(int variant, const float* diff, int64_t n_total, const float* B, int E, int d, float beta,
-                         float* loss_out, cudaStream_t s) {
+}  // extern "C"
+namespace pntf {
+int finalize_loss(int variant, const float* diff, int64_t n_total, const float* B, int E, int d, float beta,
+                  float* loss_out, cudaStream_t s) {
   prof_start(KC_FINALIZE, s);
   loss_finalize_kernel<<<1, 1024, 0, s>>>(diff, n_total, B, E * d * kNumFreq, variant == PNTF_LOSS_MULTI, beta, loss_out);
   prof_stop(s);
   return launch_check("loss_finalize");
 }
+}  // namespace pntf
+extern "C" {
 
 int pntf_loss_fwd(int variant, const float* params, const float* B, const float* coords, const float* speed, int E,
                   int64_t N, int d, float alpha, float beta, float gamma, float* diff, float* loss_out, int prec,

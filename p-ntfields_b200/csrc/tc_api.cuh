@@ -3,7 +3,20 @@
 #include <cstddef>
 #include <cstdint>
 
+#include <cuda_runtime.h>
+
 namespace pntf {
+
+// helpers defined in capi.cu
+enum { KC_PACK = 0, KC_FORWARD, KC_REVERSE, KC_DW, KC_FINALIZE, KC_ADAMW, KC_PLAN, KC_TC_FORWARD, KC_TC_REVERSE,
+       KC_TC_DW, KC_COUNT };
+int fail(int code, const char* fmt, ...);
+void prof_start(int cls, cudaStream_t s);
+void prof_stop(cudaStream_t s);
+int launch_check(const char* what);
+int sm_count();
+int finalize_loss(int variant, const float* diff, int64_t n_total, const float* B, int E, int d, float beta,
+                  float* loss_out, cudaStream_t s);
 
 size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes);
 

@@ -138,6 +138,55 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) 
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+// NC consecutive fp32 columns of this thread's lane (NC = 8, 16, 32).  The wait lists the destination
+// registers as in/out operands so that no use of them can be scheduled before it.
+template <int NC> __device__ __forceinline__ void tmem_ld(uint32_t taddr, float* v);
+template <int NC> __device__ __forceinline__ void tmem_st(uint32_t taddr, const float* v);   // needs tmem_st_wait()
+template <> __device__ __forceinline__ void tmem_ld<8>(uint32_t taddr, float* v) {
+  uint32_t r[8];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[0]),"=r"(r[1]),"=r"(r[2]),"=r"(r[3]),"=r"(r[4]),"=r"(r[5]),"=r"(r[6]),"=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]),"+r"(r[1]),"+r"(r[2]),"+r"(r[3]),"+r"(r[4]),"+r"(r[5]),"+r"(r[6]),"+r"(r[7]) : : "memory");
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
+}
+template <> __device__ __forceinline__ void tmem_st<8>(uint32_t taddr, const float* v) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(__float_as_uint(v[0])),"r"(__float_as_uint(v[1])),"r"(__float_as_uint(v[2])),"r"(__float_as_uint(v[3])),"r"(__float_as_uint(v[4])),"r"(__float_as_uint(v[5])),"r"(__float_as_uint(v[6])),"r"(__float_as_uint(v[7]))
+               : "memory");
+}
+template <> __device__ __forceinline__ void tmem_ld<16>(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : "=r"(r[0]),"=r"(r[1]),"=r"(r[2]),"=r"(r[3]),"=r"(r[4]),"=r"(r[5]),"=r"(r[6]),"=r"(r[7]),"=r"(r[8]),"=r"(r[9]),"=r"(r[10]),"=r"(r[11]),"=r"(r[12]),"=r"(r[13]),"=r"(r[14]),"=r"(r[15])
+               : "r"(taddr)
+               : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]),"+r"(r[1]),"+r"(r[2]),"+r"(r[3]),"+r"(r[4]),"+r"(r[5]),"+r"(r[6]),"+r"(r[7]),"+r"(r[8]),"+r"(r[9]),"+r"(r[10]),"+r"(r[11]),"+r"(r[12]),"+r"(r[13]),"+r"(r[14]),"+r"(r[15]) : : "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+template <> __device__ __forceinline__ void tmem_st<16>(uint32_t taddr, const float* v) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr), "r"(__float_as_uint(v[0])),"r"(__float_as_uint(v[1])),"r"(__float_as_uint(v[2])),"r"(__float_as_uint(v[3])),"r"(__float_as_uint(v[4])),"r"(__float_as_uint(v[5])),"r"(__float_as_uint(v[6])),"r"(__float_as_uint(v[7])),"r"(__float_as_uint(v[8])),"r"(__float_as_uint(v[9])),"r"(__float_as_uint(v[10])),"r"(__float_as_uint(v[11])),"r"(__float_as_uint(v[12])),"r"(__float_as_uint(v[13])),"r"(__float_as_uint(v[14])),"r"(__float_as_uint(v[15]))
+               : "memory");
+}
+template <> __device__ __forceinline__ void tmem_ld<32>(uint32_t taddr, float* v) {
+  uint32_t r[32];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+               : "=r"(r[0]),"=r"(r[1]),"=r"(r[2]),"=r"(r[3]),"=r"(r[4]),"=r"(r[5]),"=r"(r[6]),"=r"(r[7]),"=r"(r[8]),"=r"(r[9]),"=r"(r[10]),"=r"(r[11]),"=r"(r[12]),"=r"(r[13]),"=r"(r[14]),"=r"(r[15]),"=r"(r[16]),"=r"(r[17]),"=r"(r[18]),"=r"(r[19]),"=r"(r[20]),"=r"(r[21]),"=r"(r[22]),"=r"(r[23]),"=r"(r[24]),"=r"(r[25]),"=r"(r[26]),"=r"(r[27]),"=r"(r[28]),"=r"(r[29]),"=r"(r[30]),"=r"(r[31])
+               : "r"(taddr)
+               : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]),"+r"(r[1]),"+r"(r[2]),"+r"(r[3]),"+r"(r[4]),"+r"(r[5]),"+r"(r[6]),"+r"(r[7]),"+r"(r[8]),"+r"(r[9]),"+r"(r[10]),"+r"(r[11]),"+r"(r[12]),"+r"(r[13]),"+r"(r[14]),"+r"(r[15]),"+r"(r[16]),"+r"(r[17]),"+r"(r[18]),"+r"(r[19]),"+r"(r[20]),"+r"(r[21]),"+r"(r[22]),"+r"(r[23]),"+r"(r[24]),"+r"(r[25]),"+r"(r[26]),"+r"(r[27]),"+r"(r[28]),"+r"(r[29]),"+r"(r[30]),"+r"(r[31]) : : "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+template <> __device__ __forceinline__ void tmem_st<32>(uint32_t taddr, const float* v) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr), "r"(__float_as_uint(v[0])),"r"(__float_as_uint(v[1])),"r"(__float_as_uint(v[2])),"r"(__float_as_uint(v[3])),"r"(__float_as_uint(v[4])),"r"(__float_as_uint(v[5])),"r"(__float_as_uint(v[6])),"r"(__float_as_uint(v[7])),"r"(__float_as_uint(v[8])),"r"(__float_as_uint(v[9])),"r"(__float_as_uint(v[10])),"r"(__float_as_uint(v[11])),"r"(__float_as_uint(v[12])),"r"(__float_as_uint(v[13])),"r"(__float_as_uint(v[14])),"r"(__float_as_uint(v[15])),"r"(__float_as_uint(v[16])),"r"(__float_as_uint(v[17])),"r"(__float_as_uint(v[18])),"r"(__float_as_uint(v[19])),"r"(__float_as_uint(v[20])),"r"(__float_as_uint(v[21])),"r"(__float_as_uint(v[22])),"r"(__float_as_uint(v[23])),"r"(__float_as_uint(v[24])),"r"(__float_as_uint(v[25])),"r"(__float_as_uint(v[26])),"r"(__float_as_uint(v[27])),"r"(__float_as_uint(v[28])),"r"(__float_as_uint(v[29])),"r"(__float_as_uint(v[30])),"r"(__float_as_uint(v[31]))
+               : "memory");
+}
+// barrier among a subset of the CTA's warps (id 1..15)
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+
 // ---------------------------------------------------------------- operand tile geometry
 constexpr int kStageBytes = 16384;          // one weight stage: 128 x 64 fp16
 constexpr int kAtomBytes = 1024;

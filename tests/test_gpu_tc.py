@@ -1,0 +1,81 @@
+"""GPU parity tests of the tensor-core precision mode (PNTF_PREC_TC: tcgen05 kernels, fp16 operands,
+fp32 accumulation) against the CPU oracle.  Tolerances are BASELINE.json's north_star: tau within
+rel 1e-3, speed and loss within rel 1e-2; derivative columns and parameter gradients are checked in
+the max-norm."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import T, rel_err
+from oracle import pntf_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+def flat_from(P):
+    return torch.cat([P[k].reshape(-1) for k in P]).to(DEV).contiguous()
+
+
+def cu(a):
+    return T(np.asarray(a, np.float32)).to(DEV).contiguous()
+
+
+@pytest.fixture(scope="module")
+def capi():
+    from pntf import capi as c
+    c.lib()
+    return c
+
+
+def _pairs(rs, n, d):
+    # coordinates rounded through fp16 as the reference's loader does (models/data_multi.py:19)
+    return rs.uniform(-0.5, 0.5, size=(n, 2 * d)).astype(np.float16).astype(np.float32)
+
+
+def pointwise_rel(a, b):
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    return float((np.abs(a - b) / np.abs(b)).max())
+
+
+@pytest.mark.parametrize("d,N", [(3, 1), (3, 37), (3, 1000), (3, 5000), (6, 3), (6, 333), (6, 2500)])
+def test_tc_forward_vs_oracle(capi, d, N):
+    rs = np.random.RandomState(200 + d + N)
+    P = O.init_params(21)
+    Bw = (0.5 * rs.normal(size=(d, 128))).astype(np.float32)
+    c = _pairs(rs, N, d)
+    with torch.no_grad():
+        tau, dtau, ltau = O.forward(P, T(c), T(Bw), 2)
+    flat = flat_from(P)
+    t2, d2, l2 = capi.forward(capi.MODE_LAPLACE, flat, cu(Bw).view(1, d, 128), cu(c), 1, N, d, prec=capi.PREC_TC)
+    assert pointwise_rel(t2.cpu(), tau[:, 0]) < 1e-3
+    assert rel_err(d2.cpu(), dtau) < 1e-2
+    assert rel_err(l2.cpu(), ltau) < 3e-2
+    t1, d1, _ = capi.forward(capi.MODE_GRAD, flat, cu(Bw).view(1, d, 128), cu(c), 1, N, d, prec=capi.PREC_TC)
+    assert pointwise_rel(t1.cpu(), tau[:, 0]) < 1e-3
+    assert rel_err(d1.cpu(), dtau) < 1e-2
+    t0, _, _ = capi.forward(capi.MODE_VALUE, flat, cu(Bw).view(1, d, 128), cu(c), 1, N, d, prec=capi.PREC_TC)
+    assert pointwise_rel(t0.cpu(), tau[:, 0]) < 1e-3
+
+
+@pytest.mark.parametrize("d,variant,E,N", [(3, "multi", 2, 777), (6, "single", 1, 300)])
+def test_tc_loss_vs_oracle(capi, d, variant, E, N):
+    rs = np.random.RandomState(31 + d)
+    P = O.init_params(5)
+    Bw = (0.5 * rs.normal(size=(E, d, 128))).astype(np.float32)
+    c = np.stack([_pairs(rs, N, d) for _ in range(E)])
+    s = rs.uniform(0.1, 1.0, size=(E, N, 2)).astype(np.float32)
+    alpha, beta, gamma = 0.8, 2.5, 1e-3
+    s_int = alpha * s + 1 - alpha
+    if variant == "multi":
+        loss, loss_n, diff, _ = O.loss_and_grads(P, T(c), T(s_int), T(Bw), beta, gamma, "multi")
+    else:
+        loss, loss_n, diff, _ = O.loss_and_grads(P, T(c[0]), T(s_int[0]), T(Bw[0]), beta, gamma, "single")
+    v = capi.LOSS_MULTI if variant == "multi" else capi.LOSS_SINGLE
+    lo, df = capi.loss(v, flat_from(P), cu(Bw), cu(c).view(E * N, 2 * d), cu(s).view(E * N, 2), E, N, d, alpha, beta,
+                       gamma, prec=capi.PREC_TC)
+    assert abs(lo[0].item() - loss.item()) / abs(loss.item()) < 1e-2
+    assert abs(lo[1].item() - loss_n.item()) / abs(loss_n.item()) < 1e-2
+    assert rel_err(df.cpu(), diff.reshape(-1)) < 1e-2
