@@ -245,8 +245,8 @@ __device__ __forceinline__ void epi_publish(uint64_t* tile_ready) {
 
 // MMA issue of one layer: NH accumulator halves x KS stages of 64 input features.
 //   acc_col: first accumulator column; accumulate_first: accumulator pre-loaded with the skip.
-template <int S>
-__device__ __forceinline__ void mma_layer(TcCtl<S>* ctl, uint32_t ring_addr, uint32_t act_addr, uint32_t tmem_base,
+template <int S, class CTL>
+__device__ __forceinline__ void mma_layer(CTL* ctl, uint32_t ring_addr, uint32_t act_addr, uint32_t tmem_base,
                                           int acc_col, int nh, int ks_count, bool accumulate_first, uint32_t& it) {
   const uint32_t idesc = make_idesc(128, kRows, false, true);
   for (int h = 0; h < nh; ++h) {
@@ -322,7 +322,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
           tc_fence_after();
           if constexpr (TRAIN) {
             const LayerDesc L = layer_desc(l);
-            bulk_s2g(a.st.X[l] + size_t(ltile) * L.K * 256, act, uint32_t(L.K) * 256);
+            if (l < 13) bulk_s2g(a.st.X[l] + size_t(ltile) * L.K * 256, act, uint32_t(L.K) * 256);
             if (l >= 1) {
               const int Mp = layer_desc(l - 1).M;
               bulk_s2g(a.st.Y[l - 1] + size_t(ltile) * Mp * 256, yst, uint32_t(Mp) * 256);

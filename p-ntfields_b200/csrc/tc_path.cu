@@ -2,7 +2,9 @@
 // tcgen05 kernels.  Called from the C-ABI entry points in capi.cu.
 #include "../../include/pntf_b200.h"
 #include "tc_api.cuh"
+#include "tc_dw.cuh"
 #include "tc_forward.cuh"
+#include "tc_reverse.cuh"
 
 namespace pntf {
 
@@ -41,10 +43,107 @@ static int tc_launch_forward(const TcFwdArgs& a, cudaStream_t s) {
   return launch_check("tc_forward");
 }
 
+// training stash bytes per tile: X_l and Y_l (= Ybar_l) tile images of layers 0..12 + the fp32 output rows
+static size_t stash_tile_bytes() {
+  size_t s = 0;
+  for (int l = 0; l <= 12; ++l) s += size_t(layer_desc(l).K + layer_desc(l).M) * 256;
+  return s + kRows * sizeof(float);
+}
+static int tc_tile_pairs(int d) { return d <= 3 ? TcCfg<3, 2>::P : TcCfg<6, 2>::P; }
+constexpr size_t kImgBytes = ((kFwdImgBytes + kRevImgBytes + 255) / 256) * 256;
+
 size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes) {
-  (void)E; (void)N; (void)d; (void)budget_bytes;
-  if (op == PNTF_OP_LOSS_BWD) return 0;   // reverse kernels: not built yet
-  return align256(kFwdImgBytes) + 256;
+  if (op != PNTF_OP_LOSS_BWD) return align256(kFwdImgBytes) + 256;
+  const size_t P = tc_tile_pairs(d);
+  const size_t ntiles = (size_t(E) * size_t(N) + P - 1) / P;
+  if (budget_bytes == 0) budget_bytes = size_t(16) << 30;
+  size_t tiles = budget_bytes / stash_tile_bytes();
+  if (tiles > ntiles) tiles = ntiles;
+  if (tiles < 1) tiles = 1;
+  return kImgBytes + tiles * stash_tile_bytes() + 256;
+}
+
+static void tc_carve_stash(TcStash& st, uint8_t* base, size_t tiles) {
+  size_t off = 0;
+  for (int l = 0; l <= 12; ++l) {
+    st.X[l] = base + off; off += tiles * layer_desc(l).K * 256;
+    st.Y[l] = base + off; off += tiles * layer_desc(l).M * 256;
+    st.G[l] = st.Y[l];     // the reverse kernel overwrites Y_l with Ybar_l
+  }
+  st.X[13] = nullptr; st.Y[13] = nullptr; st.G[13] = nullptr;
+  st.y13 = reinterpret_cast<float*>(base + off);
+  st.g13 = nullptr;
+}
+
+// work units of the weight-gradient kernel: (layer, 128-feature half), CTAs proportional to the bytes a
+// unit streams per tile (32 KB of Ybar + K*256 B of X)
+static DwUnits make_dw_units(int sms) {
+  DwUnits u{};
+  int n = 0, cta = 0;
+  for (int l = 0; l <= 12; ++l)
+    for (int h = 0; h < (layer_desc(l).M + 127) / 128; ++h) {
+      u.l[n] = l; u.h[n] = h; u.cta_begin[n] = cta;
+      int c = (layer_desc(l).K == 256) ? 8 : 6;
+      if (sms < 142) c = (c * sms) / 142 > 0 ? (c * sms) / 142 : 1;
+      cta += c;
+      ++n;
+    }
+  u.n = n;
+  u.cta_begin[n] = cta;
+  return u;
+}
+
+template <int D>
+static int tc_loss_bwd(int variant, const float* params, const float* B, const float* coords, const float* speed, int E,
+                       int64_t N, float alpha, float beta, float gamma, float* diff, float* grad_params, uint8_t* ws,
+                       size_t ws_bytes, cudaStream_t s) {
+  using C = TcCfg<D, 2>;
+  const int64_t n_total = int64_t(E) * N;
+  uint8_t* fimg = ws;
+  uint8_t* rimg = ws + kFwdImgBytes;
+  uint8_t* stash = ws + kImgBytes;
+  if (ws_bytes < kImgBytes + stash_tile_bytes()) return fail(PNTF_ERR_WORKSPACE, "workspace too small for one tile");
+  int64_t chunk_tiles = int64_t((ws_bytes - kImgBytes) / stash_tile_bytes());
+  const int64_t ntiles_all = (n_total + C::P - 1) / C::P;
+  if (chunk_tiles > ntiles_all) chunk_tiles = ntiles_all;
+  if (int rc = tc_pack(params, fimg, rimg, s)) return rc;
+  auto kf = tc_forward_kernel<D, 2, true, TC_TAIL_LOSS>;
+  auto kr = tc_reverse_kernel<D>;
+  const size_t smem_f = fwd_smem_bytes(true), smem_r = 2 * size_t(kTileBytes) + 5 * size_t(kStageBytes) + 1024;
+  const size_t smem_d = size_t(kDwStages) * kDwStageBytes + 1024;
+  if (int rc = tc_set_smem(kf, smem_f)) return rc;
+  if (int rc = tc_set_smem(kr, smem_r)) return rc;
+  if (int rc = tc_set_smem(tc_dw_kernel, smem_d)) return rc;
+  const DwUnits units = make_dw_units(sm_count());
+  const float out_scale = float(double(beta) / (double(E) * double(N)) / double(kGradScale));
+  for (int64_t t0 = 0; t0 < ntiles_all; t0 += chunk_tiles) {
+    const int64_t tiles = (ntiles_all - t0 < chunk_tiles) ? (ntiles_all - t0) : chunk_tiles;
+    const int64_t begin = t0 * C::P;
+    const int64_t count = (n_total - begin < tiles * C::P) ? (n_total - begin) : tiles * C::P;
+    TcRevArgs r{};
+    TcFwdArgs& a = r.f;
+    a.params = params; a.wimg = fimg; a.B = B; a.coords = coords; a.speed = speed;
+    a.n_total = n_total; a.n_per_env = N; a.pair_begin = begin; a.pair_count = count;
+    a.diff = diff; a.single_variant = (variant == PNTF_LOSS_SINGLE); a.alpha = alpha; a.gamma = gamma;
+    tc_carve_stash(a.st, stash, size_t(tiles));
+    r.rimg = rimg; r.grad = grad_params; r.out_scale = out_scale;
+    const int grid = int(tiles < sm_count() ? tiles : sm_count());
+    prof_start(KC_TC_FORWARD, s);
+    kf<<<grid, kTcThreads, smem_f, s>>>(a);
+    prof_stop(s);
+    if (int rc = launch_check("tc_forward(train)")) return rc;
+    prof_start(KC_TC_REVERSE, s);
+    kr<<<grid, kTcThreads, smem_r, s>>>(r);
+    prof_stop(s);
+    if (int rc = launch_check("tc_reverse")) return rc;
+    TcDwArgs dw{};
+    dw.st = a.st; dw.units = units; dw.ntiles = tiles; dw.grad = grad_params; dw.out_scale = out_scale;
+    prof_start(KC_TC_DW, s);
+    tc_dw_kernel<<<units.cta_begin[units.n], kTcThreads, smem_d, s>>>(dw);
+    prof_stop(s);
+    if (int rc = launch_check("tc_dw")) return rc;
+  }
+  return PNTF_OK;
 }
 
 static int tc_check_ws(void* workspace, size_t workspace_bytes, size_t need) {
@@ -77,10 +176,17 @@ int tc_forward(int mode, int grad_flavour, const float* params, const float* B, 
 int tc_loss(int with_grad, int variant, const float* params, const float* B, const float* coords, const float* speed,
             int E, int64_t N, int d, float alpha, float beta, float gamma, float* diff, float* loss_out,
             float* grad_params, void* workspace, size_t workspace_bytes, void* stream) {
-  (void)grad_params;
-  if (with_grad) return fail(PNTF_ERR_UNSUPPORTED, "tensor-core reverse pass not built yet");
-  if (int rc = tc_check_ws(workspace, workspace_bytes, kFwdImgBytes)) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (with_grad) {
+    if (int rc = tc_check_ws(workspace, workspace_bytes, kImgBytes + stash_tile_bytes())) return rc;
+    int rc = (d == 3) ? tc_loss_bwd<3>(variant, params, B, coords, speed, E, N, alpha, beta, gamma, diff, grad_params,
+                                       static_cast<uint8_t*>(workspace), workspace_bytes, s)
+                      : tc_loss_bwd<6>(variant, params, B, coords, speed, E, N, alpha, beta, gamma, diff, grad_params,
+                                       static_cast<uint8_t*>(workspace), workspace_bytes, s);
+    if (rc) return rc;
+    return finalize_loss(variant, diff, int64_t(E) * N, B, E, d, beta, loss_out, s);
+  }
+  if (int rc = tc_check_ws(workspace, workspace_bytes, kFwdImgBytes)) return rc;
   uint8_t* img = static_cast<uint8_t*>(workspace);
   if (int rc = tc_pack(params, img, nullptr, s)) return rc;
   TcFwdArgs a{};

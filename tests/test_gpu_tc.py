@@ -79,3 +79,43 @@ def test_tc_loss_vs_oracle(capi, d, variant, E, N):
     assert abs(lo[0].item() - loss.item()) / abs(loss.item()) < 1e-2
     assert abs(lo[1].item() - loss_n.item()) / abs(loss_n.item()) < 1e-2
     assert rel_err(df.cpu(), diff.reshape(-1)) < 1e-2
+
+
+@pytest.mark.parametrize("d,variant,E,N,budget_tiles", [(3, "multi", 2, 203, 0), (3, "multi", 1, 2500, 100),
+                                                        (6, "single", 1, 150, 0), (6, "single", 1, 1300, 0)])
+def test_tc_param_grads_vs_oracle_autograd(capi, d, variant, E, N, budget_tiles):
+    """Model.Loss + backward on the tensor cores (forward with stash, reverse sweep, dW contraction);
+    budget_tiles > 0 forces several chunks inside one pntf_loss_bwd call."""
+    rs = np.random.RandomState(17 + d + N)
+    P = O.init_params(5)
+    Bw = (0.5 * rs.normal(size=(E, d, 128))).astype(np.float32)
+    c = np.stack([_pairs(rs, N, d) for _ in range(E)])
+    s = rs.uniform(0.1, 1.0, size=(E, N, 2)).astype(np.float32)
+    alpha, beta, gamma = 0.8, 2.5, 1e-3
+    s_int = alpha * s + 1 - alpha
+    if variant == "multi":
+        loss, loss_n, diff, grads = O.loss_and_grads(P, T(c), T(s_int), T(Bw), beta, gamma, "multi")
+    else:
+        loss, loss_n, diff, grads = O.loss_and_grads(P, T(c[0]), T(s_int[0]), T(Bw[0]), beta, gamma, "single")
+    flat = flat_from(P)
+    grad = torch.zeros_like(flat)
+    v = capi.LOSS_MULTI if variant == "multi" else capi.LOSS_SINGLE
+    budget = 0
+    if budget_tiles:
+        one = capi.workspace_bytes(capi.OP_LOSS_BWD, 1, 1, d, capi.PREC_TC)
+        two = capi.workspace_bytes(capi.OP_LOSS_BWD, 1, 1 + (8 if d == 3 else 4), d, capi.PREC_TC)
+        budget = (two - one) * budget_tiles
+    lo, df = capi.loss(v, flat, cu(Bw), cu(c).view(E * N, 2 * d), cu(s).view(E * N, 2), E, N, d, alpha, beta, gamma,
+                       grad_out=grad, prec=capi.PREC_TC, budget=budget)
+    assert abs(lo[0].item() - loss.item()) / abs(loss.item()) < 1e-2
+    assert rel_err(df.cpu(), diff.reshape(-1)) < 1e-2
+    from pntf.params import tensor_offsets, tensor_shapes
+    offs, shapes = tensor_offsets(), tensor_shapes()
+    g = grad.cpu()
+    for k, ref in grads.items():
+        n = int(np.prod(shapes[k]))
+        gk = g[offs[k]:offs[k] + n].view(shapes[k])
+        if ref is None:
+            assert bool((gk == 0).all())
+        else:
+            assert rel_err(gk, ref) < 2e-2, (k, rel_err(gk, ref))
