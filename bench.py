@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--prec", default=os.environ.get("PNTF_BENCH_PREC", "fp32"), choices=["tc", "fp32"])
+    ap.add_argument("--prec", default=os.environ.get("PNTF_BENCH_PREC", "tc"), choices=["tc", "fp32"])
     ap.add_argument("--d", type=int, default=3, choices=[3, 6])
     ap.add_argument("--pairs", type=int, default=1 << 20, help="pairs per GPU per step")
     ap.add_argument("--envs", type=int, default=1)
@@ -338,7 +338,7 @@ def run_b200(args):
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-           "dtype": "bf16 tensor-core operands, f32 accumulate/master" if prec == "tc" else "f32",
+           "dtype": "f16 tensor-core operands, f32 accumulate/master" if prec == "tc" else "f32",
            "data": "synthetic", "config": workload_config(args, prec), "clocks": clocks, "e2e": e2e,
            "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu, "kernels": kernels,
            "final_loss_n": final_loss}
