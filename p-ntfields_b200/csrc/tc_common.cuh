@@ -41,12 +41,13 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug traps (launch error) instead of hanging the GPU.
+// Bounded wait: a protocol bug traps (launch error) instead of hanging the GPU.  try_wait itself
+// suspends the thread for a hardware-defined interval, so the loop is not a hot spin.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
+  uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) __trap();
+    if (++spins > (1u << 28)) __trap();
   }
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
@@ -68,6 +69,9 @@ __device__ __forceinline__ void bulk_s2g(void* gmem_dst, const void* smem_src, u
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all committed bulk stores have finished READING shared memory
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// all but the N most recent bulk-store groups have finished reading shared memory
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // ---------------------------------------------------------------- tcgen05 / TMEM
@@ -212,6 +216,29 @@ __device__ __forceinline__ void st_chunk(uint8_t* tile, int k, int nb, int c, co
   uint4 q;
   q.x = pack_h2(v[0], v[1]); q.y = pack_h2(v[2], v[3]); q.z = pack_h2(v[4], v[5]); q.w = pack_h2(v[6], v[7]);
   *reinterpret_cast<uint4*>(tile + act_chunk_off(k, nb, c)) = q;
+}
+
+// same, addressed by a shared-window byte address with the per-thread part of the swizzle hoisted:
+// line = address of the 128-byte line of feature k in row block nb, kx = k & 7, c = chunk 0..7
+__device__ __forceinline__ uint32_t act_line_addr(uint32_t tile_addr, int k, int nb) {
+  return tile_addr + uint32_t(((k >> 3) * 2 + nb) * kAtomBytes + (k & 7) * 128);
+}
+__device__ __forceinline__ void sts_chunk(uint32_t line, int kx, int c, const float* v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(line + uint32_t(((c ^ kx) & 7) << 4)), "r"(pack_h2(v[0], v[1])),
+               "r"(pack_h2(v[2], v[3])), "r"(pack_h2(v[4], v[5])), "r"(pack_h2(v[6], v[7]))
+               : "memory");
+}
+__device__ __forceinline__ void lds_chunk(uint32_t line, int kx, int c, float* v) {
+  uint32_t q[4];
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(q[0]), "=r"(q[1]), "=r"(q[2]), "=r"(q[3])
+               : "r"(line + uint32_t(((c ^ kx) & 7) << 4))
+               : "memory");
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __half22float2(*reinterpret_cast<const __half2*>(&q[i]));
+    v[2 * i] = t.x;
+    v[2 * i + 1] = t.y;
+  }
 }
 
 }  // namespace tc

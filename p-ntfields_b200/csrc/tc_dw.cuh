@@ -27,13 +27,14 @@ struct TcDwArgs {
 
 constexpr int kDwStageBytes = 128 * 256 + 256 * 256;   // Ybar half tile + X tile
 constexpr int kDwStages = 2;
+constexpr int kDwThreads = 320;                         // 8 drain warps + loader warp 8 + MMA warp 9
 
 struct TcDwCtl {
   uint64_t full[kDwStages], empty[kDwStages], done;
   uint32_t tmem_base;
 };
 
-__global__ void __launch_bounds__(kTcThreads, 1) tc_dw_kernel(const TcDwArgs a) {
+__global__ void __launch_bounds__(kDwThreads, 1) tc_dw_kernel(const TcDwArgs a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ TcDwCtl ctl;
@@ -44,8 +45,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_dw_kernel(const TcDwArgs a) 
   const int l = a.units.l[u], h = a.units.h[u];
   const int rank = int(blockIdx.x) - a.units.cta_begin[u];
   const int ncta = a.units.cta_begin[u + 1] - a.units.cta_begin[u];
-  const LayerDesc L = layer_desc(l);
-  const int K = L.K;
+  const int K = c_K[l], M = c_M[l];
   const int64_t my_tiles = (a.ntiles > rank) ? (a.ntiles - rank + ncta - 1) / ncta : 0;
 
   if (tid == 0) {
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_dw_kernel(const TcDwArgs a) 
         mbar_wait(&ctl.empty[slot], ph ^ 1);
         mbar_arrive_expect_tx(&ctl.full[slot], 128 * 256 + xbytes);
         uint8_t* dst = smem + slot * kDwStageBytes;
-        bulk_g2s(dst, a.st.G[l] + (size_t(tile) * L.M + size_t(h) * 128) * 256, 128 * 256, &ctl.full[slot]);
+        bulk_g2s(dst, a.st.G[l] + (size_t(tile) * M + size_t(h) * 128) * 256, 128 * 256, &ctl.full[slot]);
         bulk_g2s(dst + 128 * 256, a.st.X[l] + size_t(tile) * xbytes, xbytes, &ctl.full[slot]);
       }
     }
@@ -95,8 +95,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_dw_kernel(const TcDwArgs a) 
     tc_fence_after();
     const int m = tid & 127, half = tid >> 7;
     const uint32_t lane_base = tmem_base + (uint32_t((warp & 3) * 32) << 16);
-    float* dst = a.grad + L.w + size_t(h * 128 + m) * K;
-    const bool row_ok = (h * 128 + m) < L.M;
+    float* dst = a.grad + c_w[l] + size_t(h * 128 + m) * K;
+    const bool row_ok = (h * 128 + m) < M;
     const int kc = K / 2;
     for (int c0 = half * kc; c0 < (half + 1) * kc; c0 += 32) {
       float v[32];

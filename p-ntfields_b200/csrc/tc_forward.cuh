@@ -6,9 +6,18 @@
 // accumulators with tcgen05.ld, apply bias / residual skip / softplus rules and write the next
 // layer's fp16 operand tile back to shared memory.  The residual skips stay in fp32: the block input
 // is pre-loaded into the accumulator of the block's second layer with tcgen05.st.
-//   warps 0..7 : epilogue (thread = TMEM lane = output feature, warps 0-3 rows 0..63, warps 4-7 rows 64..127)
-//   warp  8    : weight-stage producer (cp.async.bulk L2 -> shared memory ring)
-//   warp  9    : MMA issuer (+ bulk stores of the training stash)
+//   warps 0..15 : epilogue; thread = TMEM lane (= output feature within a 128-feature half) x 32-row
+//                 quarter (lane quarter = warp % 4, row quarter = warp / 4)
+//   warp  16    : weight-stage producer (cp.async.bulk L2 -> shared memory ring)
+//   warp  17    : MMA issuer (+ bulk stores of the training stash)
+// Pipelining inside a tile: operand tiles and accumulators are handed over per 128-feature half
+// (mbarriers xr[h] / ar[h]), so the issuer starts layer l+1 on input features 0..127 while the epilogue
+// still produces features 128..255 of layer l, and the epilogue starts on output half 0 while half 1
+// is still being multiplied.
+// Training stash (TRAIN): the operand tile X_l of every layer (l = 0..13) is bulk-stored as is; the
+// reverse kernel recovers the activation gates from X_{l+1} = act(Y_l) (s = 1 - exp(-10 a)), so the
+// pre-activations are not stashed, except the encoder outputs Y_5 (input of the combine) and the fp32
+// rows of the output layer.
 // Reference: NN.out_laplace, models/model_res_sigmoid.py:676-820 (models/model_res_sigmoid_multi.py:710-848);
 // NN.out_grad S:513-613; Model.Loss S:869-936 / M:897-951.
 #pragma once
@@ -22,11 +31,10 @@ namespace tc {
 enum { TC_TAIL_NONE = 0, TC_TAIL_LOSS = 1, TC_TAIL_FIELD = 2 };
 
 struct TcStash {
-  uint8_t* X[kNumLayers];   // fp16 operand-tile images of the layer inputs, [tile][K_l * 256 B]
-  uint8_t* Y[kNumLayers];   // fp16 tile images of the pre-activations (bias / skip included), layers 0..12
-  uint8_t* G[kNumLayers];   // fp16 tile images of the pre-activation adjoints (reverse kernel), layers 0..12
+  uint8_t* X[kNumLayers];   // fp16 operand-tile images of the layer inputs, [tile][K_l * 256 B], l = 0..13
+  uint8_t* Y5;              // fp16 tile images of the encoder outputs (pre-combine), [tile][128 * 256 B]
+  uint8_t* G[kNumLayers];   // fp16 tile images of the pre-activation adjoints (reverse kernel), l = 0..12
   float* y13;               // [tile][128] fp32 pre-activation rows of the output layer
-  float* g13;               // [tile][128] fp32 adjoints of the output layer's pre-activation
 };
 
 struct TcFwdArgs {
@@ -84,131 +92,154 @@ __device__ __forceinline__ void act_unit(float* y, bool compat) {
   }
 }
 
-// write NC consecutive rows (starting at row block nb, chunk c0) of feature f as fp16
-template <int NC>
-__device__ __forceinline__ void st_cols(uint8_t* tile, int f, int nb, int c0, const float* v) {
-#pragma unroll
-  for (int j = 0; j < NC / 8; ++j) st_chunk(tile, f, nb, c0 + j, v + 8 * j);
+// Position of an epilogue thread: TMEM lane (feature within a half), 32-row quarter, and the hoisted
+// parts of the operand-tile addressing for its rows.
+struct EpiPos {
+  int lane;         // 0..127
+  int rq;           // row quarter 0..3 (rows 32*rq .. 32*rq+31)
+  int nb, cb;       // 64-row block and first 8-row chunk inside it
+  uint32_t tmem;    // TMEM address of (lane quarter, column 0)
+};
+__device__ __forceinline__ EpiPos epi_pos(uint32_t tmem_base) {
+  EpiPos p;
+  const int warp = threadIdx.x >> 5;
+  p.lane = (warp & 3) * 32 + (threadIdx.x & 31);
+  p.rq = warp >> 2;
+  p.nb = p.rq >> 1;
+  p.cb = (p.rq & 1) * 4;
+  p.tmem = tmem_base + (uint32_t((warp & 3) * 32) << 16);
+  return p;
 }
 
-// Epilogue of one hidden layer.  Accumulator columns: acc_col + h*128 + row.
+// store the thread's 32 rows of feature f as fp16 (4 chunks)
+__device__ __forceinline__ void st_rows32(uint32_t act_addr, const EpiPos& p, int f, const float* v) {
+  const uint32_t line = act_line_addr(act_addr, f, p.nb);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) sts_chunk(line, f & 7, p.cb + j, v + 8 * j);
+}
+// same image, straight to global memory (stash tiles that have no shared-memory staging)
+__device__ __forceinline__ void st_rows32_global(uint8_t* tile, const EpiPos& p, int f, const float* v) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) st_chunk(tile, f, p.nb, p.cb + j, v + 8 * j);
+}
+
+// Epilogue of one 128-feature half of a hidden layer for the thread's 32 rows.
 //   ENC: a pair's CGP columns are two endpoint units of CEP columns (D derivative columns each),
 //   otherwise one unit of CGP columns (2D derivative columns).
 //   PRELOAD: also store the fp32 result to accumulator pre_col (residual skip of the next block).
-//   TRAIN: also write the pre-activations to the Y staging tile.
-template <class C, int M, bool ENC, bool PRELOAD, bool TRAIN>
-__device__ __forceinline__ void epi_hidden(uint32_t tmem_lane_base, int acc_col, int pre_col,
-                                           const float* __restrict__ bias, uint8_t* act, uint8_t* yst, bool compat) {
+template <class C, bool ENC, bool PRELOAD>
+__device__ __forceinline__ void epi_hidden_half(const EpiPos& p, int acc_col, int pre_col, int f, float b, uint32_t act_addr,
+                                                bool compat) {
   constexpr int CGP = C::CGP, CEP = C::CEP;
-  const int lane = threadIdx.x & 127, half = (threadIdx.x >> 7) & 1;
-#pragma unroll 1
-  for (int h = 0; h < M / 128; ++h) {
-    const int f = h * 128 + lane;
-    const float b = __ldg(bias + f);
-#pragma unroll 1
-    for (int pp = 0; pp < C::PH; ++pp) {
-      const int row0 = half * 64 + pp * CGP;
-      float v[CGP];
-      tmem_ld<CGP>(tmem_lane_base + acc_col + h * 128 + row0, v);
-      if constexpr (ENC) {
-        v[0] += b;
-        v[CEP] += b;
-        if constexpr (TRAIN) st_cols<CGP>(yst, f, half, (pp * CGP) >> 3, v);
-        act_unit<C::D, C::ORDER>(v, compat);
-        act_unit<C::D, C::ORDER>(v + CEP, compat);
-      } else {
-        v[0] += b;
-        if constexpr (TRAIN) st_cols<CGP>(yst, f, half, (pp * CGP) >> 3, v);
-        act_unit<2 * C::D, C::ORDER>(v, false);
-      }
-      st_cols<CGP>(act, f, half, (pp * CGP) >> 3, v);
-      if constexpr (PRELOAD) tmem_st<CGP>(tmem_lane_base + pre_col + h * 128 + row0, v);
+  float v[32];
+  tmem_ld<32>(p.tmem + acc_col + 32 * p.rq, v);
+#pragma unroll
+  for (int u = 0; u < 32 / CGP; ++u) {
+    float* y = v + u * CGP;
+    if constexpr (ENC) {
+      y[0] += b;
+      y[CEP] += b;
+      act_unit<C::D, C::ORDER>(y, compat);
+      act_unit<C::D, C::ORDER>(y + CEP, compat);
+    } else {
+      y[0] += b;
+      act_unit<2 * C::D, C::ORDER>(y, false);
     }
   }
-  if constexpr (PRELOAD) tmem_st_wait();
+  st_rows32(act_addr, p, f, v);
+  if constexpr (PRELOAD) {
+    tmem_st<32>(p.tmem + pre_col + 32 * p.rq, v);
+    tmem_st_wait();
+  }
 }
 
-// Epilogue of encoder layer 5 (no activation) fused with the symmetric combine (S:724-787): reads the
-// two endpoint encodings of feature `lane`, writes smooth-max (feature lane) and smooth-min (feature
-// 128+lane) with their derivative columns, and pre-loads both into the skip accumulator.
-template <class C, bool TRAIN>
-__device__ __forceinline__ void epi_combine(uint32_t tmem_lane_base, int acc_col, int pre_col,
-                                            const float* __restrict__ bias, uint8_t* act, uint8_t* yst) {
-  constexpr int CGP = C::CGP, CEP = C::CEP, D = C::D;
-  const int lane = threadIdx.x & 127, half = (threadIdx.x >> 7) & 1;
-  const float b = __ldg(bias + lane);
-#pragma unroll 1
-  for (int pp = 0; pp < C::PH; ++pp) {
-    const int row0 = half * 64 + pp * CGP;
-    float v[CGP];
-    tmem_ld<CGP>(tmem_lane_base + acc_col + row0, v);
-    v[0] += b;
-    v[CEP] += b;
-    if constexpr (TRAIN) st_cols<CGP>(yst, lane, half, (pp * CGP) >> 3, v);
-    const float* u = v;
-    const float* w = v + CEP;
-    float omax[CGP], omin[CGP];
+// symmetric combine of one pair (S:724-787): u, w = the two endpoint encodings of a feature (CEP columns
+// each); writes the smooth-max (MAXSIDE) or smooth-min output columns (CGP) to o.
+template <class C, bool MAXSIDE>
+__device__ __forceinline__ void combine_unit(const float* u, const float* w, float* o) {
+  constexpr int CGP = C::CGP, D = C::D;
 #pragma unroll
-    for (int c = 0; c < CGP; ++c) { omax[c] = 0.f; omin[c] = 0.f; }
-    const float dlt = u[0] - w[0];
-    const float e = __expf(-10.0f * fabsf(dlt));
-    const float tail = 0.1f * __logf(1.0f + e);
-    omax[0] = fmaxf(u[0], w[0]) + tail;
-    omin[0] = fminf(u[0], w[0]) - tail;
-    if constexpr (C::ORDER >= 1) {
-      const float inv = __fdividef(1.0f, 1.0f + e);
-      const float s0 = (dlt >= 0.f) ? inv : e * inv;
-      const float s1 = 1.0f - s0;
-      const float q = 10.0f * s0 * s1;
+  for (int c = 0; c < CGP; ++c) o[c] = 0.f;
+  const float dlt = u[0] - w[0];
+  const float e = __expf(-10.0f * fabsf(dlt));
+  const float tail = 0.1f * __logf(1.0f + e);
+  o[0] = MAXSIDE ? fmaxf(u[0], w[0]) + tail : fminf(u[0], w[0]) - tail;
+  if constexpr (C::ORDER >= 1) {
+    const float inv = __fdividef(1.0f, 1.0f + e);
+    const float s0 = (dlt >= 0.f) ? inv : e * inv;
+    const float s1 = 1.0f - s0;
+    const float q = MAXSIDE ? 10.0f * s0 * s1 : -10.0f * s0 * s1;
+    const float ga = MAXSIDE ? s0 : s1, gb = MAXSIDE ? s1 : s0;   // gates of the start / goal side
 #pragma unroll
-      for (int i = 0; i < D; ++i) {
-        const float da = u[1 + i], db = w[1 + i];
-        omax[1 + i] = da * s0;
-        omax[1 + D + i] = db * s1;
-        omin[1 + i] = da * s1;
-        omin[1 + D + i] = db * s0;
-        if constexpr (C::ORDER >= 2) {
-          const float la = u[1 + D + i], lb = w[1 + D + i];
-          const float qa = q * da * da, qb = q * db * db;
-          omax[1 + 2 * D + i] = qa + la * s0;
-          omax[1 + 3 * D + i] = qb + lb * s1;
-          omin[1 + 2 * D + i] = -qa + la * s1;
-          omin[1 + 3 * D + i] = -qb + lb * s0;
-        }
+    for (int i = 0; i < D; ++i) {
+      const float da = u[1 + i], db = w[1 + i];
+      o[1 + i] = da * ga;
+      o[1 + D + i] = db * gb;
+      if constexpr (C::ORDER >= 2) {
+        o[1 + 2 * D + i] = fmaf(q * da, da, u[1 + D + i] * ga);
+        o[1 + 3 * D + i] = fmaf(q * db, db, w[1 + D + i] * gb);
       }
     }
-    st_cols<CGP>(act, lane, half, (pp * CGP) >> 3, omax);
-    st_cols<CGP>(act, 128 + lane, half, (pp * CGP) >> 3, omin);
-    tmem_st<CGP>(tmem_lane_base + pre_col + row0, omax);
-    tmem_st<CGP>(tmem_lane_base + pre_col + 128 + row0, omin);
   }
+}
+
+// Epilogue of encoder layer 5 (no activation) fused with the symmetric combine: reads the two endpoint
+// encodings of feature `lane`, writes smooth-max (feature lane) and smooth-min (feature 128+lane) with
+// their derivative columns, and pre-loads both into the skip accumulator.  y5 != nullptr: also writes the
+// encoder outputs (bias included) to the stash tile.
+template <class C>
+__device__ __forceinline__ void epi_combine(const EpiPos& p, int acc_col, int pre_col, float b, uint32_t act_addr, uint8_t* y5) {
+  constexpr int CGP = C::CGP, CEP = C::CEP;
+  float v[32], o[32];
+  tmem_ld<32>(p.tmem + acc_col + 32 * p.rq, v);
+#pragma unroll
+  for (int u = 0; u < 32 / CGP; ++u) {
+    v[u * CGP] += b;
+    v[u * CGP + CEP] += b;
+  }
+  if (y5 != nullptr) st_rows32_global(y5, p, p.lane, v);
+#pragma unroll
+  for (int u = 0; u < 32 / CGP; ++u) combine_unit<C, true>(v + u * CGP, v + u * CGP + CEP, o + u * CGP);
+  st_rows32(act_addr, p, p.lane, o);
+  tmem_st<32>(p.tmem + pre_col + 32 * p.rq, o);
+#pragma unroll
+  for (int u = 0; u < 32 / CGP; ++u) combine_unit<C, false>(v + u * CGP, v + u * CGP + CEP, o + u * CGP);
+  st_rows32(act_addr, p, 128 + p.lane, o);
+  tmem_st<32>(p.tmem + pre_col + 128 + 32 * p.rq, o);
   tmem_st_wait();
 }
 
-// Fourier features of both endpoints of every pair (S:204-210, M:199-213) into the layer-0 operand tile.
+// Fourier features of both endpoints of the thread's pairs (S:204-210, M:199-213) into the layer-0 operand tile.
+// thread = (frequency k, row quarter).
 template <class C>
-__device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>& ts, uint8_t* act) {
+__device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>& ts, uint32_t act_addr) {
   constexpr int CGP = C::CGP, CEP = C::CEP, D = C::D;
-  const int k = threadIdx.x & 127, half = (threadIdx.x >> 7) & 1;
-#pragma unroll 1
-  for (int pp = 0; pp < C::PH; ++pp) {
-    const int p = half * C::PH + pp;
-    const float* Bp = a.B + int64_t(ts.env[p]) * D * kNumFreq + k;
+  EpiPos p;
+  p.lane = threadIdx.x & 127;
+  p.rq = threadIdx.x >> 7;
+  p.nb = p.rq >> 1;
+  p.cb = (p.rq & 1) * 4;
+  p.tmem = 0;
+  const int k = p.lane;
+  float vs[32], vc[32];
+#pragma unroll
+  for (int c = 0; c < 32; ++c) { vs[c] = 0.f; vc[c] = 0.f; }
+#pragma unroll
+  for (int u = 0; u < 32 / CGP; ++u) {
+    const int pr = p.rq * (32 / CGP) + u;
+    const float* Bp = a.B + int64_t(ts.env[pr]) * D * kNumFreq + k;
     float w[D];
 #pragma unroll
     for (int i = 0; i < D; ++i) w[i] = 6.2831855f * __ldg(Bp + i * kNumFreq);
-    float vs[CGP], vc[CGP];
-#pragma unroll
-    for (int c = 0; c < CGP; ++c) { vs[c] = 0.f; vc[c] = 0.f; }
 #pragma unroll
     for (int side = 0; side < 2; ++side) {
       float proj = 0.f;
 #pragma unroll
-      for (int i = 0; i < D; ++i) proj = fmaf(ts.x[p][side * D + i], w[i], proj);
+      for (int i = 0; i < D; ++i) proj = fmaf(ts.x[pr][side * D + i], w[i], proj);
       float sn, cs;
       sincosf(proj, &sn, &cs);
-      float* us = vs + side * CEP;
-      float* uc = vc + side * CEP;
+      float* us = vs + u * CGP + side * CEP;
+      float* uc = vc + u * CGP + side * CEP;
       us[0] = sn;
       uc[0] = cs;
       if constexpr (C::ORDER >= 1) {
@@ -223,79 +254,81 @@ __device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>
         }
       }
     }
-    st_cols<CGP>(act, k, half, (pp * CGP) >> 3, vs);
-    st_cols<CGP>(act, 128 + k, half, (pp * CGP) >> 3, vc);
   }
+  st_rows32(act_addr, p, k, vs);
+  st_rows32(act_addr, p, 128 + k, vc);
 }
 
 // shared-memory control block
 template <int S>
 struct TcCtl {
-  uint64_t full[S], empty[S];
-  uint64_t tile_ready, acc_ready;
+  uint64_t full[S], empty[S];   // weight ring
+  uint64_t xr[2];               // operand-tile half h complete (all epilogue threads arrive)
+  uint64_t ar[2];               // accumulator half h complete (tcgen05.commit)
   uint32_t tmem_base;
 };
 
-// all epilogue threads: the operand tile (and TMEM pre-loads) of the next layer are complete
-__device__ __forceinline__ void epi_publish(uint64_t* tile_ready) {
+// all epilogue threads: half h of the next operand tile (and its TMEM pre-loads) is complete
+__device__ __forceinline__ void epi_publish(uint64_t* bar) {
   fence_proxy_async();
   tc_fence_before();
-  mbar_arrive(tile_ready);
+  mbar_arrive(bar);
 }
 
-// MMA issue of one layer: NH accumulator halves x KS stages of 64 input features.
-//   acc_col: first accumulator column; accumulate_first: accumulator pre-loaded with the skip.
+// MMA issue of one (contraction half kh, output half h) block: 2 stages x 4 UMMAs.
 template <int S, class CTL>
-__device__ __forceinline__ void mma_layer(CTL* ctl, uint32_t ring_addr, uint32_t act_addr, uint32_t tmem_base,
-                                          int acc_col, int nh, int ks_count, bool accumulate_first, uint32_t& it) {
+__device__ __forceinline__ void mma_block(CTL* ctl, uint32_t ring_addr, uint32_t opnd_addr, uint32_t d_tmem, int kh,
+                                          bool accumulate_first, uint32_t& it) {
   const uint32_t idesc = make_idesc(128, kRows, false, true);
-  for (int h = 0; h < nh; ++h) {
-    for (int ks = 0; ks < ks_count; ++ks) {
-      const uint32_t slot = it % S, ph = (it / S) & 1;
-      mbar_wait(&ctl->full[slot], ph);
-      tc_fence_after();
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const uint64_t ad = make_desc(ring_addr + slot * kStageBytes + j * 32, 16, 1024);
-        const uint64_t bd = make_desc(act_addr + (ks * 4 + j) * 2 * kActSBO, kActLBO, kActSBO);
-        umma_f16(tmem_base + acc_col + h * 128, ad, bd, idesc, (accumulate_first || ks > 0 || j > 0) ? 1u : 0u);
-      }
-      umma_commit(&ctl->empty[slot]);
-      ++it;
+  for (int s2 = 0; s2 < 2; ++s2) {
+    const uint32_t slot = it % S, ph = (it / S) & 1;
+    mbar_wait(&ctl->full[slot], ph);
+    tc_fence_after();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint64_t ad = make_desc(ring_addr + slot * kStageBytes + j * 32, 16, 1024);
+      const uint64_t bd = make_desc(opnd_addr + ((kh * 2 + s2) * 4 + j) * 2 * kActSBO, kActLBO, kActSBO);
+      umma_f16(d_tmem, ad, bd, idesc, (accumulate_first || s2 > 0 || j > 0) ? 1u : 0u);
     }
+    umma_commit(&ctl->empty[slot]);
+    ++it;
   }
 }
+
+constexpr int kFwdRing = 8;                 // weight ring depth of the forward kernel
 
 template <int D, int ORDER, bool TRAIN, int TAIL>
 __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdArgs a) {
   using C = TcCfg<D, ORDER>;
-  constexpr int S = TRAIN ? 5 : 8;            // weight ring depth
+  constexpr int S = kFwdRing;
   constexpr int CGP = C::CGP, P = C::P;
   constexpr int ACC_A = 0, ACC_B = 256;       // TMEM accumulator regions (columns)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* act = smem;
-  uint8_t* yst = TRAIN ? smem + kTileBytes : nullptr;
-  uint8_t* ring = smem + (TRAIN ? 2 : 1) * kTileBytes;
+  uint8_t* ring = smem + kTileBytes;
   __shared__ TcCtl<S> ctl;
-  __shared__ TcTile<C> ts;
-  __shared__ float y13s[kRows];
+  __shared__ TcTile<C> ts[2];
+  __shared__ float y13s[2][kRows];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane_id = tid & 31;
   if (tid == 0) {
     for (int i = 0; i < S; ++i) { mbar_init(&ctl.full[i], 1); mbar_init(&ctl.empty[i], 1); }
-    mbar_init(&ctl.tile_ready, kEpiThreads);
-    mbar_init(&ctl.acc_ready, 1);
+    mbar_init(&ctl.xr[0], kEpiThreads);
+    mbar_init(&ctl.xr[1], kEpiThreads);
+    mbar_init(&ctl.ar[0], 1);
+    mbar_init(&ctl.ar[1], 1);
     fence_barrier_init();
   }
-  if (warp == 9) tmem_alloc(&ctl.tmem_base, 512);
+  if (warp == kMmaWarp) tmem_alloc(&ctl.tmem_base, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = ctl.tmem_base;
   const int64_t ntiles = (a.pair_count + P - 1) / P;
 
-  if (warp == 8) {
+  if (warp == kProducerWarp) {
     // ------------------------------------------------------------- weight-stage producer
     if (lane_id == 0) {
       uint32_t it = 0;
@@ -309,163 +342,195 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
         }
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == kMmaWarp) {
     // ------------------------------------------------------------- MMA issuer
     if (lane_id == 0) {
-      uint32_t it = 0, nlayer = 0;
+      uint32_t it = 0, nx0 = 0, nx1 = 0;
       const uint32_t ring_addr = smem_u32(ring), act_addr = smem_u32(act);
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int64_t ltile = tile;   // stash slot of this tile (tiles are local to the launch)
 #pragma unroll 1
         for (int l = 0; l < kNumLayers; ++l) {
-          mbar_wait(&ctl.tile_ready, nlayer & 1);
-          tc_fence_after();
-          if constexpr (TRAIN) {
-            const LayerDesc L = layer_desc(l);
-            if (l < 13) bulk_s2g(a.st.X[l] + size_t(ltile) * L.K * 256, act, uint32_t(L.K) * 256);
-            if (l >= 1) {
-              const int Mp = layer_desc(l - 1).M;
-              bulk_s2g(a.st.Y[l - 1] + size_t(ltile) * Mp * 256, yst, uint32_t(Mp) * 256);
+          const int K = c_K[l], KH = K >> 7, MH = halves(c_M[l]);
+          const bool skip = c_fwd_skip[l] != 0;   // accumulate onto the pre-loaded residual skip
+          const uint32_t acc = tmem_base + (skip ? ACC_B : ACC_A);
+#pragma unroll 1
+          for (int kh = 0; kh < KH; ++kh) {
+            if (kh == 0) { mbar_wait(&ctl.xr[0], nx0 & 1); ++nx0; }
+            else { mbar_wait(&ctl.xr[1], nx1 & 1); ++nx1; }
+            tc_fence_after();
+            if constexpr (TRAIN) {
+              bulk_s2g(a.st.X[l] + size_t(tile) * K * 256 + size_t(kh) * kHalfTileBytes, act + kh * kHalfTileBytes,
+                       kHalfTileBytes);
+              bulk_commit();
             }
-            bulk_commit();
+#pragma unroll 1
+            for (int h = 0; h < MH; ++h) {
+              mma_block<S>(&ctl, ring_addr, act_addr, acc + h * 128, kh, skip || kh > 0, it);
+              if (kh == KH - 1) {
+                // the epilogue of output half h overwrites features [128h, 128h+128) of the operand tile:
+                // the stash store of that half must have finished reading it
+                if constexpr (TRAIN) {
+                  if (h == 0 && MH == 2 && KH == 2) bulk_wait_read<1>();
+                  else bulk_wait_read<0>();
+                }
+                umma_commit(&ctl.ar[h]);
+              }
+            }
           }
-          // accumulator region: second layers of the residual blocks accumulate onto the pre-loaded skip
-          const bool skip = (l == 2 || l == 4 || l == 7 || l == 9 || l == 11);
-          mma_layer<S>(&ctl, ring_addr, act_addr, tmem_base, skip ? ACC_B : ACC_A, fwd_mh(l), fwd_ks(l), skip, it);
-          if constexpr (TRAIN) bulk_wait_read0();
-          umma_commit(&ctl.acc_ready);
-          ++nlayer;
         }
       }
       if constexpr (TRAIN) bulk_wait0();
     }
   } else {
     // ------------------------------------------------------------- epilogue warps
-    const uint32_t lane_base = tmem_base + (uint32_t((warp & 3) * 32) << 16);
+    const EpiPos p = epi_pos(tmem_base);
+    const uint32_t act_addr = smem_u32(act);
     const float* prm = a.params;
-    uint32_t nacc = 0;
+    uint32_t nar0 = 0, nar1 = 0;
     const bool compat = a.compat != 0;
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const int64_t pair0 = a.pair_begin + tile * P;
-      if (tid < P) {
-        const int64_t pair = pair0 + tid;
-        const bool valid = pair < a.pair_begin + a.pair_count && pair < a.n_total;
-        ts.valid[tid] = valid;
-        ts.env[tid] = valid ? int(pair / a.n_per_env) : 0;
+    // coordinates of the CTA's first two tiles (later tiles are fetched two tiles ahead by the tail threads)
+    auto load_tile = [&](int64_t tile, TcTile<C>& t) {
+      const int64_t pair = a.pair_begin + tile * P + tid;
+      const bool valid = tile < ntiles && pair < a.pair_begin + a.pair_count && pair < a.n_total;
+      t.valid[tid] = valid;
+      t.env[tid] = valid ? int(pair / a.n_per_env) : 0;
 #pragma unroll
-        for (int i = 0; i < 2 * D; ++i) ts.x[tid][i] = valid ? __ldg(a.coords + pair * 2 * D + i) : 0.f;
-      }
-      named_bar_sync(1, kEpiThreads);
-      fourier_tile<C>(a, ts, act);
-      epi_publish(&ctl.tile_ready);
-#define PNTF_WAIT_ACC()                        \
-  mbar_wait(&ctl.acc_ready, nacc & 1);         \
-  ++nacc;                                      \
-  tc_fence_after();
+      for (int i = 0; i < 2 * D; ++i) t.x[tid][i] = valid ? __ldg(a.coords + pair * 2 * D + i) : 0.f;
+    };
+    if (tid < P) {
+      load_tile(blockIdx.x, ts[0]);
+      load_tile(int64_t(blockIdx.x) + gridDim.x, ts[1]);
+    }
+    named_bar_sync(1, kEpiThreads);
+    int par = 0;
+#define PNTF_WAIT_ACC0() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); }
+#define PNTF_WAIT_ACC1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); }
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
+      const int64_t pair0 = a.pair_begin + tile * P;
+      fourier_tile<C>(a, ts[par], act_addr);
+      epi_publish(&ctl.xr[0]);
+      epi_publish(&ctl.xr[1]);
       // encoder: L0 ; {L1, L2(+skip)} ; {L3, L4(+skip)} ; L5 + combine
-      PNTF_WAIT_ACC();
-      epi_hidden<C, 128, true, true, TRAIN>(lane_base, ACC_A, ACC_B, prm + layer_desc(0).b, act, yst, compat);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_ACC();
-      epi_hidden<C, 128, true, false, TRAIN>(lane_base, ACC_A, 0, prm + layer_desc(1).b, act, yst, false);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_ACC();
-      epi_hidden<C, 128, true, true, TRAIN>(lane_base, ACC_B, ACC_B, prm + layer_desc(2).b, act, yst, false);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_ACC();
-      epi_hidden<C, 128, true, false, TRAIN>(lane_base, ACC_A, 0, prm + layer_desc(3).b, act, yst, false);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_ACC();
-      epi_hidden<C, 128, true, false, TRAIN>(lane_base, ACC_B, 0, prm + layer_desc(4).b, act, yst, false);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_ACC();
-      epi_combine<C, TRAIN>(lane_base, ACC_A, ACC_B, prm + layer_desc(5).b, act, yst);
-      epi_publish(&ctl.tile_ready);
+      PNTF_WAIT_ACC0();
+      epi_hidden_half<C, true, true>(p, ACC_A, ACC_B, p.lane, __ldg(prm + c_b[0] + p.lane), act_addr, compat);
+      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT_ACC0();
+      epi_hidden_half<C, true, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[1] + p.lane), act_addr, false);
+      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT_ACC0();
+      epi_hidden_half<C, true, true>(p, ACC_B, ACC_B, p.lane, __ldg(prm + c_b[2] + p.lane), act_addr, false);
+      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT_ACC0();
+      epi_hidden_half<C, true, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[3] + p.lane), act_addr, false);
+      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT_ACC0();
+      epi_hidden_half<C, true, false>(p, ACC_B, 0, p.lane, __ldg(prm + c_b[4] + p.lane), act_addr, false);
+      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT_ACC0();
+      epi_combine<C>(p, ACC_A, ACC_B, __ldg(prm + c_b[5] + p.lane), act_addr,
+                     TRAIN ? a.st.Y5 + size_t(tile) * kHalfTileBytes : nullptr);
+      epi_publish(&ctl.xr[0]);
+      epi_publish(&ctl.xr[1]);
       // generator: 3 x {La, Lb(+skip)} ; L12 ; L13
 #pragma unroll 1
       for (int ii = 0; ii < 3; ++ii) {
-        PNTF_WAIT_ACC();
-        epi_hidden<C, 256, false, false, TRAIN>(lane_base, ACC_A, 0, prm + layer_desc(6 + 2 * ii).b, act, yst, false);
-        epi_publish(&ctl.tile_ready);
-        PNTF_WAIT_ACC();
-        if (ii < 2)
-          epi_hidden<C, 256, false, true, TRAIN>(lane_base, ACC_B, ACC_B, prm + layer_desc(7 + 2 * ii).b, act, yst, false);
-        else
-          epi_hidden<C, 256, false, false, TRAIN>(lane_base, ACC_B, 0, prm + layer_desc(7 + 2 * ii).b, act, yst, false);
-        epi_publish(&ctl.tile_ready);
+        const float* ba = prm + c_b[6 + 2 * ii] + p.lane;
+        const float* bb = prm + c_b[7 + 2 * ii] + p.lane;
+        PNTF_WAIT_ACC0();
+        epi_hidden_half<C, false, false>(p, ACC_A, 0, p.lane, __ldg(ba), act_addr, false);
+        epi_publish(&ctl.xr[0]);
+        PNTF_WAIT_ACC1();
+        epi_hidden_half<C, false, false>(p, ACC_A + 128, 0, 128 + p.lane, __ldg(ba + 128), act_addr, false);
+        epi_publish(&ctl.xr[1]);
+        if (ii < 2) {
+          PNTF_WAIT_ACC0();
+          epi_hidden_half<C, false, true>(p, ACC_B, ACC_B, p.lane, __ldg(bb), act_addr, false);
+          epi_publish(&ctl.xr[0]);
+          PNTF_WAIT_ACC1();
+          epi_hidden_half<C, false, true>(p, ACC_B + 128, ACC_B + 128, 128 + p.lane, __ldg(bb + 128), act_addr, false);
+          epi_publish(&ctl.xr[1]);
+        } else {
+          PNTF_WAIT_ACC0();
+          epi_hidden_half<C, false, false>(p, ACC_B, 0, p.lane, __ldg(bb), act_addr, false);
+          epi_publish(&ctl.xr[0]);
+          PNTF_WAIT_ACC1();
+          epi_hidden_half<C, false, false>(p, ACC_B + 128, 0, 128 + p.lane, __ldg(bb + 128), act_addr, false);
+          epi_publish(&ctl.xr[1]);
+        }
       }
-      PNTF_WAIT_ACC();
-      epi_hidden<C, 128, false, false, TRAIN>(lane_base, ACC_A, 0, prm + layer_desc(12).b, act, yst, false);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_ACC();
-#undef PNTF_WAIT_ACC
+      PNTF_WAIT_ACC0();
+      epi_hidden_half<C, false, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[12] + p.lane), act_addr, false);
+      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT_ACC0();
       // output layer: lane 0 of the accumulator holds y13 for all rows
       if ((warp & 3) == 0) {
-        const int half = warp >> 2;
-#pragma unroll 1
-        for (int pp = 0; pp < C::PH; ++pp) {
-          float v[CGP];
-          tmem_ld<CGP>(lane_base + ACC_A + half * 64 + pp * CGP, v);
-          if (lane_id == 0) {
+        float v[32];
+        tmem_ld<32>(p.tmem + ACC_A + 32 * p.rq, v);
+        if (lane_id == 0) {
 #pragma unroll
-            for (int c = 0; c < CGP; ++c) y13s[half * 64 + pp * CGP + c] = v[c];
-          }
+          for (int c = 0; c < 32; ++c) y13s[par][32 * p.rq + c] = v[c];
         }
       }
       tc_fence_before();
       named_bar_sync(1, kEpiThreads);
-      if (tid < P && ts.valid[tid]) {
-        const int64_t pair = pair0 + tid;
-        float y[CGP];
-#pragma unroll
-        for (int c = 0; c < CGP; ++c) y[c] = y13s[tid * CGP + c];
-        y[0] += __ldg(prm + layer_desc(13).b);
-        const ActOut o = actout_eval(y[0]);
-        const float tau = o.o;
-        float dtau[C::N1], ltau[C::N1];
-#pragma unroll
-        for (int i = 0; i < C::N1; ++i) {
-          const float dy = y[1 + i];
-          dtau[i] = dy * o.o1;
-          ltau[i] = 0.f;
-          if constexpr (ORDER >= 2) ltau[i] = fmaf(dy * dy, o.o2, y[1 + C::N1 + i] * o.o1);
-        }
-        if (a.tau) a.tau[pair] = tau;
-        if (a.dtau)
-          for (int i = 0; i < C::N1; ++i) a.dtau[pair * C::N1 + i] = dtau[i];
-        if constexpr (ORDER >= 2) {
-          if (a.ltau)
-            for (int i = 0; i < C::N1; ++i) a.ltau[pair * C::N1 + i] = ltau[i];
-        }
-        const float* x = ts.x[tid];
-        if constexpr (TAIL == TC_TAIL_LOSS && ORDER == 2) {
-          const float y0 = a.alpha * __ldg(a.speed + pair * 2) + 1.0f - a.alpha;
-          const float y1 = a.alpha * __ldg(a.speed + pair * 2 + 1) + 1.0f - a.alpha;
-          a.diff[pair] = eikonal_residual<D, false>(x, tau, dtau, ltau, y0, y1, a.gamma, a.single_variant, 0.f, nullptr,
-                                                    nullptr, nullptr);
-        }
-        if constexpr (TAIL == TC_TAIL_FIELD) {
-          if (a.field_kind == 0) a.field[pair] = field_travel_time<D>(x, tau);
-          if (a.field_kind == 1) a.field[pair] = field_speed<D>(x, tau, dtau, ltau, 0.f, false);
-          if (a.field_kind == 3) {
-            float out[2 * D];
-            field_direction<D>(x, tau, dtau, out);
-            for (int i = 0; i < 2 * D; ++i) a.field[pair * 2 * D + i] = out[i];
-          }
-          if constexpr (ORDER >= 2) {
-            if (a.field_kind == 2) a.field[pair] = field_speed<D>(x, tau, dtau, ltau, a.gamma, true);
-          }
-        }
-      }
       if constexpr (TRAIN) {
-        if (tid < kRows) a.st.y13[size_t(tile) * kRows + tid] = y13s[tid];
+        if (tid >= 128 && tid < 128 + kRows) a.st.y13[size_t(tile) * kRows + (tid - 128)] = y13s[par][tid - 128];
       }
-      // y13s / ts are rewritten only after the next tile's first named barrier
+      if (tid < P) {
+        if (ts[par].valid[tid]) {
+          const int64_t pair = pair0 + tid;
+          float y[CGP];
+#pragma unroll
+          for (int c = 0; c < CGP; ++c) y[c] = y13s[par][tid * CGP + c];
+          y[0] += __ldg(prm + c_b[13]);
+          const ActOut o = actout_eval(y[0]);
+          const float tau = o.o;
+          float dtau[C::N1], ltau[C::N1];
+#pragma unroll
+          for (int i = 0; i < C::N1; ++i) {
+            const float dy = y[1 + i];
+            dtau[i] = dy * o.o1;
+            ltau[i] = 0.f;
+            if constexpr (ORDER >= 2) ltau[i] = fmaf(dy * dy, o.o2, y[1 + C::N1 + i] * o.o1);
+          }
+          if (a.tau) a.tau[pair] = tau;
+          if (a.dtau)
+            for (int i = 0; i < C::N1; ++i) a.dtau[pair * C::N1 + i] = dtau[i];
+          if constexpr (ORDER >= 2) {
+            if (a.ltau)
+              for (int i = 0; i < C::N1; ++i) a.ltau[pair * C::N1 + i] = ltau[i];
+          }
+          const float* x = ts[par].x[tid];
+          if constexpr (TAIL == TC_TAIL_LOSS && ORDER == 2) {
+            const float y0 = a.alpha * __ldg(a.speed + pair * 2) + 1.0f - a.alpha;
+            const float y1 = a.alpha * __ldg(a.speed + pair * 2 + 1) + 1.0f - a.alpha;
+            a.diff[pair] = eikonal_residual<D, false>(x, tau, dtau, ltau, y0, y1, a.gamma, a.single_variant, 0.f, nullptr,
+                                                      nullptr, nullptr);
+          }
+          if constexpr (TAIL == TC_TAIL_FIELD) {
+            if (a.field_kind == 0) a.field[pair] = field_travel_time<D>(x, tau);
+            if (a.field_kind == 1) a.field[pair] = field_speed<D>(x, tau, dtau, ltau, 0.f, false);
+            if (a.field_kind == 3) {
+              float out[2 * D];
+              field_direction<D>(x, tau, dtau, out);
+              for (int i = 0; i < 2 * D; ++i) a.field[pair * 2 * D + i] = out[i];
+            }
+            if constexpr (ORDER >= 2) {
+              if (a.field_kind == 2) a.field[pair] = field_speed<D>(x, tau, dtau, ltau, a.gamma, true);
+            }
+          }
+        }
+        // this buffer's next user is the tile after next: fetch its coordinates now (the barrier of the
+        // next tile orders these writes before its readers)
+        load_tile(tile + 2 * int64_t(gridDim.x), ts[par]);
+      }
     }
+#undef PNTF_WAIT_ACC0
+#undef PNTF_WAIT_ACC1
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) tmem_dealloc(tmem_base, 512);
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
 }
 
 }  // namespace tc

@@ -8,6 +8,11 @@
 //     D[out-feature (TMEM lane)][row (TMEM column)] = W[out][in] * X[in][row]
 // with W streamed from L2 in 16 KB stages ([128 out] x [64 in], K-major) and the epilogue thread of
 // lane f seeing all columns of a pair contiguously.
+//
+// Stage order inside a layer (forward and reverse images alike): the contraction is split into halves
+// of 128 input features (kh); within kh come the output halves (h, 128 features each), each with its
+// two 64-feature stages.  The MMA issuer can therefore start a layer as soon as the first 128 features
+// of its operand tile exist, and the first output half completes before the second one is issued.
 // Reference arithmetic: models/model_res_sigmoid.py:629-657 (linear_laplace / act_laplace).
 #pragma once
 #include <cuda_fp16.h>
@@ -28,20 +33,34 @@ struct TcCfg {
   static constexpr int CG = 1 + NG;
   static constexpr int CGP = 2 * CEP;                               // padded columns per pair (>= CG)
   static constexpr int P = 128 / CGP;                               // pairs per tile
-  static constexpr int PH = P / 2;                                  // pairs per 64-row block
   static constexpr int N1 = 2 * D;
   static_assert(CG <= CGP, "column padding");
+  static_assert(CGP == 8 || CGP == 16 || CGP == 32, "a pair's columns must divide a 32-row quarter");
 };
 
 constexpr int kRows = 128;                  // rows (UMMA N) per tile
 constexpr int kTileBytes = 256 * kRows * 2; // activation tile: 256 features x 128 rows fp16
-constexpr int kEpiThreads = 256;            // epilogue warps 0..7
-constexpr int kTcThreads = 320;             // + producer warp 8 + MMA warp 9
+constexpr int kHalfTileBytes = kTileBytes / 2;
+constexpr int kEpiWarps = 16;
+constexpr int kEpiThreads = kEpiWarps * 32; // epilogue warps 0..15: lane quarter = warp % 4, row quarter = warp / 4
+constexpr int kTcThreads = kEpiThreads + 64;   // + producer warp 16 + MMA warp 17
+constexpr int kProducerWarp = kEpiWarps, kMmaWarp = kEpiWarps + 1;
 
-// ---- forward weight stages: layer l = ceil(M/128) halves x K/64 stages, in consumption order
-__host__ __device__ constexpr int fwd_mh(int l) { return layer_desc(l).M > 128 ? 2 : 1; }
-__host__ __device__ constexpr int fwd_ks(int l) { return layer_desc(l).K / 64; }
-__host__ __device__ constexpr int fwd_stages(int l) { return fwd_mh(l) * fwd_ks(l); }
+// per-layer run-time tables (constant memory: indexed with a run-time layer number by the issuer threads)
+static __constant__ int c_K[kNumLayers] = {256, 128, 128, 128, 128, 128, 256, 256, 256, 256, 256, 256, 256, 128};
+static __constant__ int c_M[kNumLayers] = {128, 128, 128, 128, 128, 128, 256, 256, 256, 256, 256, 256, 128, 1};
+// forward: layers whose accumulator was pre-loaded with the residual skip (second layer of a block)
+static __constant__ int c_fwd_skip[kNumLayers] = {0, 0, 1, 0, 1, 0, 0, 1, 0, 1, 0, 1, 0, 0};
+// reverse: products W_l^T Ybar_l that land on a pre-loaded skip adjoint (first layer of a block)
+static __constant__ int c_rev_skip[kNumLayers] = {0, 1, 0, 1, 0, 0, 1, 0, 1, 0, 1, 0, 0, 0};
+// offsets of the layers' weights / biases inside the flat parameter buffer (layout.cuh, execution order)
+static __constant__ int c_w[kNumLayers] = {0, 32896, 115328, 49408, 131840, 65920, 148352, 378753, 214144, 444545, 279936, 510337, 345728, 378624};
+static __constant__ int c_b[kNumLayers] = {32768, 49280, 131712, 65792, 148224, 82304, 213888, 444289, 279680, 510081, 345472, 575873, 378496, 378752};
+
+__host__ __device__ constexpr int halves(int features) { return (features + 127) / 128; }
+
+// ---- forward weight stages: layer l = (K/128) x ceil(M/128) x 2 stages
+__host__ __device__ constexpr int fwd_stages(int l) { return halves(layer_desc(l).K) * halves(layer_desc(l).M) * 2; }
 __host__ __device__ constexpr int fwd_stage_begin(int l) {
   int s = 0;
   for (int i = 0; i < l; ++i) s += fwd_stages(i);
@@ -49,10 +68,10 @@ __host__ __device__ constexpr int fwd_stage_begin(int l) {
 }
 constexpr int kFwdStages = fwd_stage_begin(kNumLayers);   // 68
 
-// ---- reverse weight stages (Xbar_l = W_l^T Ybar_l for l = 12 .. 1): K_l/128 halves x M_l/64 stages
-__host__ __device__ constexpr int rev_mh(int l) { return layer_desc(l).K / 128; }
-__host__ __device__ constexpr int rev_ks(int l) { return layer_desc(l).M / 64; }
-__host__ __device__ constexpr int rev_stages(int l) { return (l >= 1 && l <= 12) ? rev_mh(l) * rev_ks(l) : 0; }
+// ---- reverse weight stages (Xbar_l = W_l^T Ybar_l for l = 12 .. 1): contraction over M_l, output K_l
+__host__ __device__ constexpr int rev_stages(int l) {
+  return (l >= 1 && l <= 12) ? halves(layer_desc(l).M) * halves(layer_desc(l).K) * 2 : 0;
+}
 __host__ __device__ constexpr int rev_stage_begin(int l) {   // processing order 12, 11, ..., 1
   int s = 0;
   for (int i = 12; i > l; --i) s += rev_stages(i);
@@ -60,11 +79,22 @@ __host__ __device__ constexpr int rev_stage_begin(int l) {   // processing order
 }
 constexpr int kRevStages = rev_stage_begin(0);            // 62
 
+// first stage of each layer inside the images (forward: consumption order 0..13; reverse: 12..1)
+static __constant__ int c_fwd_begin[kNumLayers + 1] = {
+    fwd_stage_begin(0), fwd_stage_begin(1), fwd_stage_begin(2), fwd_stage_begin(3), fwd_stage_begin(4),
+    fwd_stage_begin(5), fwd_stage_begin(6), fwd_stage_begin(7), fwd_stage_begin(8), fwd_stage_begin(9),
+    fwd_stage_begin(10), fwd_stage_begin(11), fwd_stage_begin(12), fwd_stage_begin(13), fwd_stage_begin(14)};
+static __constant__ int c_rev_begin[kNumLayers] = {
+    rev_stage_begin(0), rev_stage_begin(1), rev_stage_begin(2), rev_stage_begin(3), rev_stage_begin(4),
+    rev_stage_begin(5), rev_stage_begin(6), rev_stage_begin(7), rev_stage_begin(8), rev_stage_begin(9),
+    rev_stage_begin(10), rev_stage_begin(11), rev_stage_begin(12), 0};
+
 constexpr size_t kFwdImgBytes = size_t(kFwdStages) * kStageBytes;
 constexpr size_t kRevImgBytes = size_t(kRevStages) * kStageBytes;
 
 // fp32 parameters -> fp16 stage images.  One thread = one 16-byte chunk (8 consecutive k) of one
-// stage row.
+// stage row.  Stage s of a layer: kh = s / (2*OH), h = (s/2) % OH, 64-feature block ks = 2*kh + s%2
+// (OH = output halves).
 __global__ void pack_images_kernel(const float* __restrict__ params, uint8_t* __restrict__ fwd_img,
                                    uint8_t* __restrict__ rev_img) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -79,24 +109,28 @@ __global__ void pack_images_kernel(const float* __restrict__ params, uint8_t* __
     int l = 0;
 #pragma unroll 1
     for (int i = 1; i < kNumLayers; ++i)
-      if (g >= fwd_stage_begin(i)) l = i;
-    const LayerDesc L = layer_desc(l);
-    const int s = g - fwd_stage_begin(l);
-    const int h = s / fwd_ks(l), ks = s % fwd_ks(l);
+      if (g >= c_fwd_begin[i]) l = i;
+    const int K = c_K[l], M = c_M[l];
+    const int s = g - c_fwd_begin[l];
+    const int oh = halves(M);
+    const int kh = s / (2 * oh), h = (s >> 1) % oh, ks = 2 * kh + (s & 1);
     const int mo = h * 128 + m;
+    const float* W = params + c_w[l];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = (mo < L.M) ? params[L.w + mo * L.K + ks * 64 + c * 8 + j] : 0.f;
+    for (int j = 0; j < 8; ++j) v[j] = (mo < M) ? W[mo * K + ks * 64 + c * 8 + j] : 0.f;
   } else {
     int l = 12;
 #pragma unroll 1
     for (int i = 11; i >= 1; --i)
-      if (g >= rev_stage_begin(i)) l = i;
-    const LayerDesc L = layer_desc(l);
-    const int s = g - rev_stage_begin(l);
-    const int h = s / rev_ks(l), ks = s % rev_ks(l);
+      if (g >= c_rev_begin[i]) l = i;
+    const int K = c_K[l];
+    const int s = g - c_rev_begin[l];
+    const int oh = halves(K);
+    const int kh = s / (2 * oh), h = (s >> 1) % oh, ks = 2 * kh + (s & 1);
     const int ko = h * 128 + m;   // output index of the transposed product = input feature of layer l
+    const float* W = params + c_w[l];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = params[L.w + (ks * 64 + c * 8 + j) * L.K + ko];
+    for (int j = 0; j < 8; ++j) v[j] = W[(ks * 64 + c * 8 + j) * K + ko];
   }
   uint4 q;
   q.x = pack_h2(v[0], v[1]); q.y = pack_h2(v[2], v[3]); q.z = pack_h2(v[4], v[5]); q.w = pack_h2(v[6], v[7]);

@@ -27,13 +27,14 @@ static int tc_pack(const float* params, uint8_t* fwd_img, uint8_t* rev_img, cuda
   return launch_check("tc_pack_images");
 }
 
-constexpr size_t fwd_smem_bytes(bool train) { return size_t(train ? 2 : 1) * kTileBytes + size_t(train ? 5 : 8) * kStageBytes + 1024; }
+constexpr size_t kFwdSmem = size_t(kTileBytes) + size_t(kFwdRing) * kStageBytes + 1024;
+constexpr size_t kRevSmem = 2 * size_t(kTileBytes) + size_t(kRevRing) * kStageBytes + (kNumBiasSlots + 132) * sizeof(float) + 1024;
 
 template <int D, int ORDER, bool TRAIN, int TAIL>
 static int tc_launch_forward(const TcFwdArgs& a, cudaStream_t s) {
   using C = TcCfg<D, ORDER>;
   auto k = tc_forward_kernel<D, ORDER, TRAIN, TAIL>;
-  const size_t smem = fwd_smem_bytes(TRAIN);
+  const size_t smem = kFwdSmem;
   if (int rc = tc_set_smem(k, smem)) return rc;
   const int64_t ntiles = (a.pair_count + C::P - 1) / C::P;
   const int grid = int(ntiles < sm_count() ? ntiles : sm_count());
@@ -43,11 +44,13 @@ static int tc_launch_forward(const TcFwdArgs& a, cudaStream_t s) {
   return launch_check("tc_forward");
 }
 
-// training stash bytes per tile: X_l and Y_l (= Ybar_l) tile images of layers 0..12 + the fp32 output rows
+// training stash bytes per tile: operand tiles X_l (l = 0..13), encoder outputs Y5, adjoint tiles Ybar_l
+// (l = 0..12) and the fp32 output rows
 static size_t stash_tile_bytes() {
   size_t s = 0;
-  for (int l = 0; l <= 12; ++l) s += size_t(layer_desc(l).K + layer_desc(l).M) * 256;
-  return s + kRows * sizeof(float);
+  for (int l = 0; l <= 13; ++l) s += size_t(layer_desc(l).K) * 256;
+  for (int l = 0; l <= 12; ++l) s += size_t(layer_desc(l).M) * 256;
+  return s + kHalfTileBytes + kRows * sizeof(float);
 }
 static int tc_tile_pairs(int d) { return d <= 3 ? TcCfg<3, 2>::P : TcCfg<6, 2>::P; }
 constexpr size_t kImgBytes = ((kFwdImgBytes + kRevImgBytes + 255) / 256) * 256;
@@ -65,14 +68,11 @@ size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes) 
 
 static void tc_carve_stash(TcStash& st, uint8_t* base, size_t tiles) {
   size_t off = 0;
-  for (int l = 0; l <= 12; ++l) {
-    st.X[l] = base + off; off += tiles * layer_desc(l).K * 256;
-    st.Y[l] = base + off; off += tiles * layer_desc(l).M * 256;
-    st.G[l] = st.Y[l];     // the reverse kernel overwrites Y_l with Ybar_l
-  }
-  st.X[13] = nullptr; st.Y[13] = nullptr; st.G[13] = nullptr;
+  for (int l = 0; l <= 13; ++l) { st.X[l] = base + off; off += tiles * layer_desc(l).K * 256; }
+  for (int l = 0; l <= 12; ++l) { st.G[l] = base + off; off += tiles * layer_desc(l).M * 256; }
+  st.G[13] = nullptr;
+  st.Y5 = base + off; off += tiles * kHalfTileBytes;
   st.y13 = reinterpret_cast<float*>(base + off);
-  st.g13 = nullptr;
 }
 
 // work units of the weight-gradient kernel: (layer, 128-feature half), CTAs proportional to the bytes a
@@ -109,7 +109,7 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
   if (int rc = tc_pack(params, fimg, rimg, s)) return rc;
   auto kf = tc_forward_kernel<D, 2, true, TC_TAIL_LOSS>;
   auto kr = tc_reverse_kernel<D>;
-  const size_t smem_f = fwd_smem_bytes(true), smem_r = 2 * size_t(kTileBytes) + 5 * size_t(kStageBytes) + 1024;
+  const size_t smem_f = kFwdSmem, smem_r = kRevSmem;
   const size_t smem_d = size_t(kDwStages) * kDwStageBytes + 1024;
   if (int rc = tc_set_smem(kf, smem_f)) return rc;
   if (int rc = tc_set_smem(kr, smem_r)) return rc;
@@ -139,7 +139,7 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     TcDwArgs dw{};
     dw.st = a.st; dw.units = units; dw.ntiles = tiles; dw.grad = grad_params; dw.out_scale = out_scale;
     prof_start(KC_TC_DW, s);
-    tc_dw_kernel<<<units.cta_begin[units.n], kTcThreads, smem_d, s>>>(dw);
+    tc_dw_kernel<<<units.cta_begin[units.n], kDwThreads, smem_d, s>>>(dw);
     prof_stop(s);
     if (int rc = launch_check("tc_dw")) return rc;
   }

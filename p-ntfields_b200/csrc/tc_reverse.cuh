@@ -1,12 +1,18 @@
 // tcgen05 reverse kernel (tensor-core precision mode): adjoint sweep of the second-order forward pass.
-// Same CTA organisation as tc_forward_kernel.  Per tile it seeds the adjoints from the Eikonal loss,
-// then walks the layers backwards: the epilogue warps read Xbar_{l+1} (adjoint of layer l's activated
-// output) from TMEM and the stashed pre-activations Y_l from shared memory, apply the activation
-// adjoint, write Ybar_l as the fp16 operand tile of the next product
+// Same CTA organisation as tc_forward_kernel (16 epilogue warps, producer warp, MMA warp; operand tiles
+// and accumulators handed over per 128-feature half).  Per tile it seeds the adjoints from the Eikonal
+// loss, then walks the layers backwards: the epilogue warps read Xbar_{l+1} (adjoint of layer l's
+// activated output) from TMEM and the stashed forward outputs X_{l+1} = act(Y_l) from shared memory,
+// apply the activation adjoint (with the gates recovered from the activated
+// values: s = 1 - exp(-10 a), dy = dx'/s, ...), write Ybar_l as the fp16 operand tile of the next product
 // Xbar_l = W_l^T Ybar_l (tcgen05.mma, transposed weight stages) and pre-load it in fp32 into the TMEM
 // accumulator that receives the residual-skip adjoint.  Every Ybar_l tile is also dumped to the stash
-// (over Y_l) for the weight-gradient contraction (tc_dw_kernel); bias gradients and the 128 -> 1 output
-// layer's weight gradient are reduced in registers.
+// for the weight-gradient contraction (tc_dw_kernel); bias gradients and the 128 -> 1 output layer's
+// weight gradient are reduced in shared memory.
+// TMEM regions: products of the second layer of a block (and layer 12) land in B / A alternately so that
+// a product never overwrites what the running epilogue still reads:
+//   12 -> B ; 11 -> A ; 10 -> B (+skip) ; 9 -> A ; 8 -> B (+skip) ; 7 -> A ; 6 -> B (+skip) ; 5 -> A ;
+//   4 -> A ; 3 -> B (+skip) ; 2 -> A ; 1 -> B (+skip)
 // The reference gets all of this from autograd (loss.backward(), models/model_res_sigmoid.py:1071).
 #pragma once
 #include "tc_forward.cuh"
@@ -23,178 +29,185 @@ struct TcRevArgs {
   float out_scale;          // beta / (E*N) / kGradScale
 };
 
-// read NC consecutive rows of feature f (fp16 -> fp32)
-template <int NC>
-__device__ __forceinline__ void ld_cols(const uint8_t* tile, int f, int nb, int c0, float* v) {
-#pragma unroll
-  for (int j = 0; j < NC / 8; ++j) {
-    const uint4 q = *reinterpret_cast<const uint4*>(tile + act_chunk_off(f, nb, c0 + j));
-    const __half2* h = reinterpret_cast<const __half2*>(&q);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float2 t = __half22float2(h[i]);
-      v[8 * j + 2 * i] = t.x;
-      v[8 * j + 2 * i + 1] = t.y;
-    }
-  }
-}
+// accumulator region of product l (1 = B) and the region the epilogue of step l reads
+static __constant__ int c_rev_acc[kNumLayers] = {0, 1, 0, 1, 0, 0, 1, 0, 1, 0, 1, 0, 1, 0};
 
-// adjoint of act_unit, in place on g (incoming: adjoints of the activated outputs), y = pre-activations
+// Adjoint of act_unit, in place on g (incoming: adjoints of the activated outputs x = (a, dx', lx') as
+// stashed by the forward pass).  With t = exp(-10 a) = 1 - s:  s'/s = 10 t,  s''/s' = 10 (1 - 2 s),
+// dy = dx'/s,  dy^2 s' = dy dx' 10 t,  ly s' = 10 t (lx' - dy^2 s').
 template <int NDER>
-__device__ __forceinline__ void act_adjoint_unit(float* g, const float* y) {
-  const FastAct a = fast_act(y[0]);
-  const float spp = 10.0f * a.sp * (1.0f - 2.0f * a.s);
-  float xb = g[0] * a.s;
+__device__ __forceinline__ void act_adjoint_unit(float* g, const float* x) {
+  const float t = __expf(-10.0f * x[0]);
+  const float s = 1.0f - t;
+  const float r = __fdividef(1.0f, fmaxf(s, 1e-6f));
+  const float t10 = 10.0f * t;
+  const float c2 = 10.0f * (1.0f - 2.0f * s);
+  float xb = g[0] * s;
 #pragma unroll
   for (int i = 0; i < NDER; ++i) {
-    const float dy = y[1 + i], ly = y[1 + NDER + i];
+    const float dxp = x[1 + i], lxp = x[1 + NDER + i];
     const float gd = g[1 + i], gl = g[1 + NDER + i];
-    xb = fmaf(gd * dy, a.sp, xb);
-    xb = fmaf(gl, fmaf(dy * dy, spp, ly * a.sp), xb);
-    g[1 + i] = fmaf(gd, a.s, gl * 2.0f * dy * a.sp);
-    g[1 + NDER + i] = gl * a.s;
+    const float d10 = dxp * t10;            // dy s'
+    const float u = dxp * r * d10;          // dy^2 s'
+    xb = fmaf(gd, d10, xb);
+    xb = fmaf(gl, fmaf(u, c2, t10 * (lxp - u)), xb);
+    g[1 + i] = fmaf(gd, s, 2.0f * gl * d10);
+    g[1 + NDER + i] = gl * s;
   }
   g[0] = xb;
 }
 
-// Ybar_l for one hidden layer.  SRC13: the incoming adjoint is the rank-1 product w13[f] * g13[row]
-// (output layer) instead of a TMEM accumulator; its weight gradient is reduced here as well.
-template <class C, int M, bool ENC, bool PRELOAD, bool SRC13>
-__device__ __forceinline__ void epi_adjoint(uint32_t tmem_lane_base, int acc_col, int pre_col, const uint8_t* ybuf,
-                                            uint8_t* gt, float* db, const float* g13s, float w13f, float& dw13) {
-  constexpr int CGP = C::CGP, CEP = C::CEP;
-  const int lane = threadIdx.x & 127, half = (threadIdx.x >> 7) & 1;
+// load the thread's 32 rows of feature f from a stash tile image in shared memory
+__device__ __forceinline__ void ld_rows32(uint32_t tile_addr, const EpiPos& p, int f, float* v) {
+  const uint32_t line = act_line_addr(tile_addr, f, p.nb);
 #pragma unroll
-  for (int h = 0; h < M / 128; ++h) {
-    const int f = h * 128 + lane;
-    float dbh = 0.f;
-#pragma unroll 1
-    for (int pp = 0; pp < C::PH; ++pp) {
-      const int row0 = half * 64 + pp * CGP;
-      float g[CGP], y[CGP];
-      if constexpr (SRC13) {
-#pragma unroll
-        for (int c = 0; c < CGP; ++c) g[c] = w13f * g13s[row0 + c];
-      } else {
-        tmem_ld<CGP>(tmem_lane_base + acc_col + h * 128 + row0, g);
-      }
-      ld_cols<CGP>(ybuf, f, half, (pp * CGP) >> 3, y);
-      if constexpr (SRC13) {
-        // X13 = act(Y12): weight gradient of the output layer, dW13[f] += sum_c g13[c] X13[f][c]
-        float x[CGP];
-#pragma unroll
-        for (int c = 0; c < CGP; ++c) x[c] = y[c];
-        act_unit<2 * C::D, C::ORDER>(x, false);
-#pragma unroll
-        for (int c = 0; c < C::CG; ++c) dw13 = fmaf(g13s[row0 + c], x[c], dw13);
-      }
-      if constexpr (ENC) {
-        act_adjoint_unit<C::D>(g, y);
-        act_adjoint_unit<C::D>(g + CEP, y + CEP);
-        dbh += g[0] + g[CEP];
-      } else {
-        act_adjoint_unit<2 * C::D>(g, y);
-        dbh += g[0];
-      }
-      st_cols<CGP>(gt, f, half, (pp * CGP) >> 3, g);
-      if constexpr (PRELOAD) tmem_st<CGP>(tmem_lane_base + pre_col + h * 128 + row0, g);
-    }
-    db[h] += dbh;
-  }
-  if constexpr (PRELOAD) tmem_st_wait();
+  for (int j = 0; j < 4; ++j) lds_chunk(line, f & 7, p.cb + j, v + 8 * j);
 }
 
-// Adjoint of the symmetric combine (S:724-787): reads the adjoints of the
-// smooth-max (feature lane) and smooth-min (feature 128+lane) outputs from the accumulator and the stashed
-// encoder outputs Y5 of both endpoints, writes Ybar5 (= adjoint of the encoder output, layer 5 has no
-// activation) for both endpoints.
-template <class C>
-__device__ __forceinline__ void epi_combine_adjoint(uint32_t tmem_lane_base, int acc_col, const uint8_t* ybuf,
-                                                    uint8_t* gt, float* db) {
-  constexpr int CGP = C::CGP, CEP = C::CEP, D = C::D;
-  const int lane = threadIdx.x & 127, half = (threadIdx.x >> 7) & 1;
-  float dbh = 0.f;
-#pragma unroll 1
-  for (int pp = 0; pp < C::PH; ++pp) {
-    const int row0 = half * 64 + pp * CGP;
-    float gmax[CGP], gmin[CGP], y[CGP], o[CGP];
-    tmem_ld<CGP>(tmem_lane_base + acc_col + row0, gmax);
-    tmem_ld<CGP>(tmem_lane_base + acc_col + 128 + row0, gmin);
-    ld_cols<CGP>(ybuf, lane, half, (pp * CGP) >> 3, y);
+// Ybar_l for one 128-feature half of a hidden layer, the thread's 32 rows.  SRC13: the incoming adjoint
+// is the rank-1 product w13[f] * g13[row] (output layer) instead of a TMEM accumulator; its weight
+// gradient is reduced here as well.  Returns the thread's bias-gradient partial sum.
+template <class C, bool ENC, bool PRELOAD, bool SRC13>
+__device__ __forceinline__ float epi_adjoint_half(const EpiPos& p, int in_col, int pre_col, int f, uint32_t x_addr,
+                                                  uint32_t gt_addr, const float* g13s, float w13f, float& dw13) {
+  constexpr int CGP = C::CGP, CEP = C::CEP;
+  float g[32], x[32];
+  if constexpr (SRC13) {
 #pragma unroll
-    for (int c = 0; c < CGP; ++c) o[c] = 0.f;
-    const float* u = y;
-    const float* v = y + CEP;
-    float* ou = o;
-    float* ov = o + CEP;
-    const float s0 = fast_sigmoid(10.0f * (u[0] - v[0]));
-    const float s1 = 1.0f - s0;
-    const float q = 10.0f * s0 * s1;
-    const float qp = 10.0f * q * (1.0f - 2.0f * s0);
-    float ub = 0.f;
-#pragma unroll
-    for (int i = 0; i < D; ++i) {
-      const float a = u[1 + i], b = v[1 + i], A = u[1 + D + i], Bq = v[1 + D + i];
-      const float dmax0 = gmax[1 + i], dmax1 = gmax[1 + D + i], dmin0 = gmin[1 + i], dmin1 = gmin[1 + D + i];
-      const float lmax0 = gmax[1 + 2 * D + i], lmax1 = gmax[1 + 3 * D + i];
-      const float lmin0 = gmin[1 + 2 * D + i], lmin1 = gmin[1 + 3 * D + i];
-      const float dl0 = lmax0 - lmin0, dl1 = lmax1 - lmin1;
-      ub += q * ((dmax0 - dmin0) * a - (dmax1 - dmin1) * b + dl0 * A - dl1 * Bq) + qp * (dl0 * a * a + dl1 * b * b);
-      ou[1 + i] = dmax0 * s0 + dmin0 * s1 + 2.0f * q * a * dl0;
-      ov[1 + i] = dmax1 * s1 + dmin1 * s0 + 2.0f * q * b * dl1;
-      ou[1 + D + i] = lmax0 * s0 + lmin0 * s1;
-      ov[1 + D + i] = lmax1 * s1 + lmin1 * s0;
-    }
-    ou[0] = gmax[0] * s0 + gmin[0] * s1 + ub;
-    ov[0] = gmax[0] * s1 + gmin[0] * s0 - ub;
-    dbh += ou[0] + ov[0];
-    st_cols<CGP>(gt, lane, half, (pp * CGP) >> 3, o);
+    for (int c = 0; c < 32; ++c) g[c] = w13f * g13s[32 * p.rq + c];
+  } else {
+    tmem_ld<32>(p.tmem + in_col + 32 * p.rq, g);
   }
-  db[0] += dbh;
+  ld_rows32(x_addr, p, f, x);
+  if constexpr (SRC13) {
+    // X13 = act(Y12) is the stashed tile itself: dW13[f] += sum_rows g13[row] X13[f][row]
+#pragma unroll
+    for (int c = 0; c < 32; ++c) dw13 = fmaf(g13s[32 * p.rq + c], x[c], dw13);
+  }
+  float db = 0.f;
+#pragma unroll
+  for (int u = 0; u < 32 / CGP; ++u) {
+    if constexpr (ENC) {
+      act_adjoint_unit<C::D>(g + u * CGP, x + u * CGP);
+      act_adjoint_unit<C::D>(g + u * CGP + CEP, x + u * CGP + CEP);
+      db += g[u * CGP] + g[u * CGP + CEP];
+    } else {
+      act_adjoint_unit<2 * C::D>(g + u * CGP, x + u * CGP);
+      db += g[u * CGP];
+    }
+  }
+  st_rows32(gt_addr, p, f, g);
+  if constexpr (PRELOAD) {
+    tmem_st<32>(p.tmem + pre_col + 32 * p.rq, g);
+    tmem_st_wait();
+  }
+  return db;
+}
+
+// Adjoint of the symmetric combine of one pair (S:724-787): gmax / gmin = adjoints
+// of the smooth-max / smooth-min outputs (CGP columns each), y = stashed encoder outputs Y5 of both
+// endpoints (CEP columns each); writes the adjoints of the two encoder outputs to o (CGP columns).
+template <class C>
+__device__ __forceinline__ void combine_adjoint_unit(const float* gmax, const float* gmin, const float* y, float* o) {
+  constexpr int CGP = C::CGP, CEP = C::CEP, D = C::D;
+#pragma unroll
+  for (int c = 0; c < CGP; ++c) o[c] = 0.f;
+  const float* u = y;
+  const float* v = y + CEP;
+  float* ou = o;
+  float* ov = o + CEP;
+  const float s0 = fast_sigmoid(10.0f * (u[0] - v[0]));
+  const float s1 = 1.0f - s0;
+  const float q = 10.0f * s0 * s1;
+  const float qp = 10.0f * q * (1.0f - 2.0f * s0);
+  float ub = 0.f;
+#pragma unroll
+  for (int i = 0; i < D; ++i) {
+    const float a = u[1 + i], b = v[1 + i], A = u[1 + D + i], Bq = v[1 + D + i];
+    const float dmax0 = gmax[1 + i], dmax1 = gmax[1 + D + i], dmin0 = gmin[1 + i], dmin1 = gmin[1 + D + i];
+    const float lmax0 = gmax[1 + 2 * D + i], lmax1 = gmax[1 + 3 * D + i];
+    const float lmin0 = gmin[1 + 2 * D + i], lmin1 = gmin[1 + 3 * D + i];
+    const float dl0 = lmax0 - lmin0, dl1 = lmax1 - lmin1;
+    ub += q * ((dmax0 - dmin0) * a - (dmax1 - dmin1) * b + dl0 * A - dl1 * Bq) + qp * (dl0 * a * a + dl1 * b * b);
+    ou[1 + i] = dmax0 * s0 + dmin0 * s1 + 2.0f * q * a * dl0;
+    ov[1 + i] = dmax1 * s1 + dmin1 * s0 + 2.0f * q * b * dl1;
+    ou[1 + D + i] = lmax0 * s0 + lmin0 * s1;
+    ov[1 + D + i] = lmax1 * s1 + lmin1 * s0;
+  }
+  ou[0] = gmax[0] * s0 + gmin[0] * s1 + ub;
+  ov[0] = gmax[0] * s1 + gmin[0] * s0 - ub;
+}
+
+// Step 5: reads the adjoints of the combine output (features lane and 128+lane) from the accumulator and
+// the stashed encoder outputs Y5, writes Ybar5 (layer 5 has no activation).  Returns the bias partial sum.
+template <class C>
+__device__ __forceinline__ float epi_combine_adjoint(const EpiPos& p, int in_col, uint32_t y_addr, uint32_t gt_addr) {
+  constexpr int CGP = C::CGP, CEP = C::CEP;
+  float y[32];
+  ld_rows32(y_addr, p, p.lane, y);
+  float db = 0.f;
+  const uint32_t line = act_line_addr(gt_addr, p.lane, p.nb);
+#pragma unroll
+  for (int u = 0; u < 32 / CGP; ++u) {
+    float gmax[CGP], gmin[CGP], o[CGP];
+    tmem_ld<CGP>(p.tmem + in_col + 32 * p.rq + u * CGP, gmax);
+    tmem_ld<CGP>(p.tmem + in_col + 128 + 32 * p.rq + u * CGP, gmin);
+    combine_adjoint_unit<C>(gmax, gmin, y + u * CGP, o);
+    db += o[0] + o[CEP];
+#pragma unroll
+    for (int j = 0; j < CGP / 8; ++j) sts_chunk(line, p.lane & 7, p.cb + u * (CGP / 8) + j, o + 8 * j);
+  }
+  return db;
 }
 
 template <int S>
 struct TcRevCtl {
   uint64_t full[S], empty[S];
-  uint64_t tile_ready, acc_ready, y_full;
+  uint64_t xr[2];     // Ybar operand-tile half complete (= stash-buffer half consumed)
+  uint64_t ar[2];     // product half complete (= operand-tile half free again)
+  uint64_t yb[2];     // stash-buffer half loaded
   uint32_t tmem_base;
 };
 
-// accumulate-onto-skip layers of the reverse sweep (their product lands on the pre-loaded skip adjoint)
-__host__ __device__ constexpr bool rev_on_skip(int l) { return l == 10 || l == 8 || l == 6 || l == 3 || l == 1; }
+constexpr int kRevRing = 5;
+constexpr int kNumBiasSlots = 2432;   // sum of M_l over l = 0..12: offsets c_db[l]
+static __constant__ int c_db[kNumLayers] = {0, 128, 256, 384, 512, 640, 768, 1024, 1280, 1536, 1792, 2048, 2304, 2432};
 
 template <int D>
 __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevArgs b) {
   using C = TcCfg<D, 2>;
-  constexpr int S = 5;
+  constexpr int S = kRevRing;
   constexpr int CGP = C::CGP, P = C::P, NG = C::N1;
   constexpr int ACC_A = 0, ACC_B = 256;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* gt = smem;                         // Ybar operand tile
-  uint8_t* ybuf = smem + kTileBytes;          // stashed pre-activations of the current layer
+  uint8_t* xbuf = smem + kTileBytes;          // stashed forward outputs of the current layer (two halves)
   uint8_t* ring = smem + 2 * kTileBytes;
+  float* sdb = reinterpret_cast<float*>(ring + S * kStageBytes);   // bias-gradient partial sums [2432] + dW13 [128] + db13
   __shared__ TcRevCtl<S> ctl;
-  __shared__ TcTile<C> ts;
   __shared__ float g13s[kRows];
   const TcFwdArgs& a = b.f;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane_id = tid & 31;
+  for (int i = tid; i < kNumBiasSlots + 129; i += kTcThreads) sdb[i] = 0.f;
   if (tid == 0) {
     for (int i = 0; i < S; ++i) { mbar_init(&ctl.full[i], 1); mbar_init(&ctl.empty[i], 1); }
-    mbar_init(&ctl.tile_ready, kEpiThreads);
-    mbar_init(&ctl.acc_ready, 1);
-    mbar_init(&ctl.y_full, 1);
+    for (int h = 0; h < 2; ++h) {
+      mbar_init(&ctl.xr[h], kEpiThreads);
+      mbar_init(&ctl.ar[h], 1);
+      mbar_init(&ctl.yb[h], 1);
+    }
     fence_barrier_init();
   }
-  if (warp == 9) tmem_alloc(&ctl.tmem_base, 512);
+  if (warp == kMmaWarp) tmem_alloc(&ctl.tmem_base, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = ctl.tmem_base;
   const int64_t ntiles = (a.pair_count + P - 1) / P;
 
-  if (warp == 8) {
+  if (warp == kProducerWarp) {
     if (lane_id == 0) {
       uint32_t it = 0;
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -207,52 +220,80 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
         }
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == kMmaWarp) {
     if (lane_id == 0) {
-      uint32_t it = 0, n = 0;
+      uint32_t it = 0, nx0 = 0, nx1 = 0;
       const uint32_t ring_addr = smem_u32(ring), gt_addr = smem_u32(gt);
-      mbar_arrive(&ctl.acc_ready);     // completion #0: the operand tile starts out free
-      if (int64_t(blockIdx.x) < ntiles) {
-        mbar_arrive_expect_tx(&ctl.y_full, 128 * 256);
-        bulk_g2s(ybuf, a.st.Y[12] + size_t(blockIdx.x) * 128 * 256, 128 * 256, &ctl.y_full);
-      }
+      // stash source of step l: the forward outputs X_{l+1} (Y5 for the combine step)
+      auto src = [&](int l, int64_t tile) -> const uint8_t* {
+        return (l == 5) ? a.st.Y5 + size_t(tile) * kHalfTileBytes
+                        : a.st.X[l + 1] + size_t(tile) * size_t(c_K[l + 1]) * 256;
+      };
+      auto load_half = [&](int l, int64_t tile, int h) {
+        mbar_arrive_expect_tx(&ctl.yb[h], kHalfTileBytes);
+        bulk_g2s(xbuf + h * kHalfTileBytes, src(l, tile) + size_t(h) * kHalfTileBytes, kHalfTileBytes, &ctl.yb[h]);
+      };
+      mbar_arrive(&ctl.ar[0]);     // completion #0: the operand tile starts out free
+      if (int64_t(blockIdx.x) < ntiles) load_half(12, blockIdx.x, 0);
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
 #pragma unroll 1
         for (int l = 12; l >= 0; --l) {
-          mbar_wait(&ctl.tile_ready, n & 1);
-          tc_fence_after();
-          const int Ml = layer_desc(l).M;
-          bulk_s2g(a.st.G[l] + size_t(tile) * Ml * 256, gt, uint32_t(Ml) * 256);
-          bulk_commit();
-          // pre-activations of the next step (all epilogue threads are done with the current ones)
+          const int M = c_M[l], MH = halves(M), OH = c_K[l] >> 7;
+          const bool skip = c_rev_skip[l] != 0;
+          const uint32_t acc = tmem_base + (c_rev_acc[l] ? ACC_B : ACC_A);
           const int ln = (l > 0) ? l - 1 : 12;
           const int64_t tn = (l > 0) ? tile : tile + gridDim.x;
-          if (tn < ntiles) {
-            const uint32_t bytes = uint32_t(layer_desc(ln).M) * 256;
-            mbar_arrive_expect_tx(&ctl.y_full, bytes);
-            bulk_g2s(ybuf, a.st.Y[ln] + size_t(tn) * bytes, bytes, &ctl.y_full);
+          const int MHn = (ln == 5) ? 1 : halves(c_M[ln]);
+#pragma unroll 1
+          for (int kh = 0; kh < MH; ++kh) {
+            if (kh == 0) { mbar_wait(&ctl.xr[0], nx0 & 1); ++nx0; }
+            else { mbar_wait(&ctl.xr[1], nx1 & 1); ++nx1; }
+            tc_fence_after();
+            bulk_s2g(a.st.G[l] + size_t(tile) * M * 256 + size_t(kh) * kHalfTileBytes, gt + kh * kHalfTileBytes,
+                     kHalfTileBytes);
+            bulk_commit();
+            // the epilogue is done with stash-buffer half kh: fetch the next step's half
+            if (tn < ntiles) {
+              if (kh < MHn) load_half(ln, tn, kh);
+              if (kh == MH - 1)
+                for (int hh = MH; hh < MHn; ++hh) load_half(ln, tn, hh);
+            }
+            if (l >= 1) {
+#pragma unroll 1
+              for (int h = 0; h < OH; ++h) {
+                mma_block<S>(&ctl, ring_addr, gt_addr, acc + h * 128, kh, skip || kh > 0, it);
+                if (kh == MH - 1) {
+                  // the next epilogue overwrites operand-tile half h: its stash store must have read it
+                  if (MH == 1 && OH == 2) {
+                    // both output halves contract over operand half 0: release it after the last block only
+                    if (h == 1) {
+                      bulk_wait_read<0>();
+                      umma_commit(&ctl.ar[0]);
+                      umma_commit(&ctl.ar[1]);
+                    }
+                  } else {
+                    if (h == 0 && MH == 2) bulk_wait_read<1>();
+                    else bulk_wait_read<0>();
+                    umma_commit(&ctl.ar[h]);
+                  }
+                }
+              }
+            } else {
+              bulk_wait_read<0>();
+              mbar_arrive(&ctl.ar[0]);
+            }
           }
-          if (l >= 1)
-            mma_layer<S>(&ctl, ring_addr, gt_addr, tmem_base, rev_on_skip(l) ? ACC_B : ACC_A, rev_mh(l), rev_ks(l),
-                         rev_on_skip(l), it);
-          bulk_wait_read0();
-          if (l >= 1) umma_commit(&ctl.acc_ready);
-          else mbar_arrive(&ctl.acc_ready);
-          ++n;
         }
       }
       bulk_wait0();
     }
   } else {
-    const uint32_t lane_base = tmem_base + (uint32_t((warp & 3) * 32) << 16);
+    const EpiPos p = epi_pos(tmem_base);
+    const uint32_t gt_addr = smem_u32(gt), x_addr = smem_u32(xbuf);
     const float* prm = a.params;
-    const int lane = tid & 127;
-    const float w13f = __ldg(prm + layer_desc(13).w + lane);
-    float dbs[19];
-#pragma unroll
-    for (int i = 0; i < 19; ++i) dbs[i] = 0.f;
-    float dw13 = 0.f, db13 = 0.f, unused = 0.f;
-    uint32_t n = 0;
+    const float w13f = __ldg(prm + c_w[13] + p.lane);
+    float dw13 = 0.f, unused = 0.f;
+    uint32_t nar0 = 0, nar1 = 0, ny0 = 0, ny1 = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int64_t pair0 = a.pair_begin + tile * P;
       // ---- loss seeds and output-activation adjoint (one thread per pair), S:890-936 / M:914-951
@@ -268,7 +309,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
           for (int i = 0; i < 2 * D; ++i) x[i] = __ldg(a.coords + pair * 2 * D + i);
 #pragma unroll
           for (int c = 0; c < CGP; ++c) y[c] = a.st.y13[size_t(tile) * kRows + tid * CGP + c];
-          y[0] += __ldg(prm + layer_desc(13).b);
+          y[0] += __ldg(prm + c_b[13]);
           const ActOut o = actout_eval(y[0]);
           float dtau[NG], ltau[NG];
 #pragma unroll
@@ -290,78 +331,81 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
             gy[1 + NG + i] = lbar[i] * o.o1;
           }
           gy[0] = yb;
-          db13 += yb;
+          atomicAdd(sdb + kNumBiasSlots + 128, yb);
         }
 #pragma unroll
         for (int c = 0; c < CGP; ++c) g13s[tid * CGP + c] = gy[c];
       }
       named_bar_sync(1, kEpiThreads);
-#define PNTF_WAIT_STEP()                     \
-  mbar_wait(&ctl.acc_ready, n & 1);          \
-  tc_fence_after();                          \
-  mbar_wait(&ctl.y_full, n & 1);             \
-  ++n;
-      // generator
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 128, false, false, true>(lane_base, 0, 0, ybuf, gt, dbs + 0, g13s, w13f, dw13);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 256, false, true, false>(lane_base, ACC_A, ACC_B, ybuf, gt, dbs + 1, nullptr, 0.f, unused);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 256, false, false, false>(lane_base, ACC_A, 0, ybuf, gt, dbs + 3, nullptr, 0.f, unused);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 256, false, true, false>(lane_base, ACC_B, ACC_B, ybuf, gt, dbs + 5, nullptr, 0.f, unused);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 256, false, false, false>(lane_base, ACC_A, 0, ybuf, gt, dbs + 7, nullptr, 0.f, unused);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 256, false, true, false>(lane_base, ACC_B, ACC_B, ybuf, gt, dbs + 9, nullptr, 0.f, unused);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 256, false, false, false>(lane_base, ACC_A, 0, ybuf, gt, dbs + 11, nullptr, 0.f, unused);
-      epi_publish(&ctl.tile_ready);
-      // combine and encoder
-      PNTF_WAIT_STEP();
-      epi_combine_adjoint<C>(lane_base, ACC_B, ybuf, gt, dbs + 13);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 128, true, true, false>(lane_base, ACC_A, ACC_B, ybuf, gt, dbs + 14, nullptr, 0.f, unused);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 128, true, false, false>(lane_base, ACC_A, 0, ybuf, gt, dbs + 15, nullptr, 0.f, unused);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 128, true, true, false>(lane_base, ACC_B, ACC_B, ybuf, gt, dbs + 16, nullptr, 0.f, unused);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 128, true, false, false>(lane_base, ACC_A, 0, ybuf, gt, dbs + 17, nullptr, 0.f, unused);
-      epi_publish(&ctl.tile_ready);
-      PNTF_WAIT_STEP();
-      epi_adjoint<C, 128, true, false, false>(lane_base, ACC_B, 0, ybuf, gt, dbs + 18, nullptr, 0.f, unused);
-      epi_publish(&ctl.tile_ready);
-#undef PNTF_WAIT_STEP
+#define PNTF_WAIT0() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; }
+#define PNTF_WAIT1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); mbar_wait(&ctl.yb[1], ny1 & 1); ++ny1; }
+#define PNTF_DB(l, h, v) atomicAdd(sdb + c_db[l] + (h) * 128 + p.lane, (v))
+      // ---- generator
+      PNTF_WAIT0();
+      PNTF_DB(12, 0, (epi_adjoint_half<C, false, false, true>(p, 0, 0, p.lane, x_addr, gt_addr, g13s, w13f, dw13)));
+      epi_publish(&ctl.xr[0]);
+#pragma unroll 1
+      for (int l = 11; l >= 6; --l) {
+        const bool second = (l & 1) != 0;      // second layer of a block: reads B, pre-loads the skip adjoint in place
+        if (second) {
+          PNTF_WAIT0();
+          PNTF_DB(l, 0, (epi_adjoint_half<C, false, true, false>(p, ACC_B, ACC_B, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
+          epi_publish(&ctl.xr[0]);
+          PNTF_WAIT1();
+          PNTF_DB(l, 1, (epi_adjoint_half<C, false, true, false>(p, ACC_B + 128, ACC_B + 128, 128 + p.lane, x_addr, gt_addr,
+                                                                  nullptr, 0.f, unused)));
+          epi_publish(&ctl.xr[1]);
+        } else {
+          PNTF_WAIT0();
+          PNTF_DB(l, 0, (epi_adjoint_half<C, false, false, false>(p, ACC_A, 0, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
+          epi_publish(&ctl.xr[0]);
+          PNTF_WAIT1();
+          PNTF_DB(l, 1, (epi_adjoint_half<C, false, false, false>(p, ACC_A + 128, 0, 128 + p.lane, x_addr, gt_addr, nullptr,
+                                                                   0.f, unused)));
+          epi_publish(&ctl.xr[1]);
+        }
+      }
+      // ---- combine (needs both halves of the adjoint of its output) and encoder
+      PNTF_WAIT0();
+      { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); }
+      PNTF_DB(5, 0, epi_combine_adjoint<C>(p, ACC_B, x_addr, gt_addr));
+      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT0();
+      PNTF_DB(4, 0, (epi_adjoint_half<C, true, true, false>(p, ACC_A, ACC_B, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
+      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT0();
+      PNTF_DB(3, 0, (epi_adjoint_half<C, true, false, false>(p, ACC_A, 0, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
+      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT0();
+      PNTF_DB(2, 0, (epi_adjoint_half<C, true, true, false>(p, ACC_B, ACC_B, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
+      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT0();
+      PNTF_DB(1, 0, (epi_adjoint_half<C, true, false, false>(p, ACC_A, 0, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
+      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT0();
+      PNTF_DB(0, 0, (epi_adjoint_half<C, true, false, false>(p, ACC_B, 0, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
+      epi_publish(&ctl.xr[0]);
+#undef PNTF_WAIT0
+#undef PNTF_WAIT1
+#undef PNTF_DB
+      // g13s is rewritten by the next tile's seeds only after every thread has left step 12 of this tile:
+      // the named barrier of the next tile comes after this tile's last publish of all threads
     }
+    atomicAdd(sdb + kNumBiasSlots + p.lane, dw13);
     // ---- bias gradients (+ output layer weight gradient) of this CTA's tiles
+    named_bar_sync(1, kEpiThreads);
     const float sc = b.out_scale;
     float* gp = b.grad;
-    atomicAdd(gp + layer_desc(12).b + lane, dbs[0] * sc);
-#pragma unroll
-    for (int j = 0; j < 6; ++j) {            // layers 11 .. 6, two feature halves each
-      const int l = 11 - j;
-      atomicAdd(gp + layer_desc(l).b + lane, dbs[1 + 2 * j] * sc);
-      atomicAdd(gp + layer_desc(l).b + 128 + lane, dbs[2 + 2 * j] * sc);
+    for (int l = 0; l <= 12; ++l) {
+      const int M = c_M[l];
+      for (int i = tid; i < M; i += kEpiThreads) atomicAdd(gp + c_b[l] + i, sdb[c_db[l] + i] * sc);
     }
-#pragma unroll
-    for (int j = 0; j < 6; ++j) atomicAdd(gp + layer_desc(5 - j).b + lane, dbs[13 + j] * sc);
-    atomicAdd(gp + layer_desc(13).w + lane, dw13 * sc);
-    if (tid < P) atomicAdd(gp + layer_desc(13).b, db13 * sc);
+    if (tid < 128) atomicAdd(gp + c_w[13] + tid, sdb[kNumBiasSlots + tid] * sc);
+    if (tid == 128) atomicAdd(gp + c_b[13], sdb[kNumBiasSlots + 128] * sc);
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) tmem_dealloc(tmem_base, 512);
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
 }
 
 }  // namespace tc
