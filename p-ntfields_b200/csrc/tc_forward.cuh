@@ -9,11 +9,14 @@
 //   warps 0..15 : epilogue; thread = TMEM lane (= output feature within a 128-feature half) x 32-row
 //                 quarter (lane quarter = warp % 4, row quarter = warp / 4)
 //   warp  16    : weight-stage producer (cp.async.bulk L2 -> shared memory ring)
-//   warp  17    : MMA issuer (+ bulk stores of the training stash)
+//   warp  17    : MMA issuer
+//   warp  18    : bulk stores of the training stash (TRAIN)
 // Pipelining inside a tile: operand tiles and accumulators are handed over per 128-feature half
 // (mbarriers xr[h] / ar[h]), so the issuer starts layer l+1 on input features 0..127 while the epilogue
 // still produces features 128..255 of layer l, and the epilogue starts on output half 0 while half 1
 // is still being multiplied.
+// Operand tiles are double-buffered (X_l lives in buffer l & 1), so an epilogue never overwrites the tile
+// the running product or stash store still reads.
 // Training stash (TRAIN): the operand tile X_l of every layer (l = 0..13) is bulk-stored as is; the
 // reverse kernel recovers the activation gates from X_{l+1} = act(Y_l) (s = 1 - exp(-10 a)), so the
 // pre-activations are not stashed, except the encoder outputs Y_5 (input of the combine) and the fp32
@@ -50,7 +53,13 @@ struct TcFwdArgs {
   float alpha, gamma;
   int compat;
   TcStash st;
+  long long* trace;         // debug (PNTF_TRACE=1): clock64 time stamps of CTA 0's third tile, else nullptr
 };
+
+// debug time stamps: slot layout [role][layer][event]
+__device__ __forceinline__ void trace_evt(long long* trace, bool on, int role, int l, int evt) {
+  if (trace != nullptr && on) trace[(role * 16 + l) * 4 + evt] = clock64();
+}
 
 template <class C>
 struct TcTile {
@@ -117,12 +126,6 @@ __device__ __forceinline__ void st_rows32(uint32_t act_addr, const EpiPos& p, in
 #pragma unroll
   for (int j = 0; j < 4; ++j) sts_chunk(line, f & 7, p.cb + j, v + 8 * j);
 }
-// same image, straight to global memory (stash tiles that have no shared-memory staging)
-__device__ __forceinline__ void st_rows32_global(uint8_t* tile, const EpiPos& p, int f, const float* v) {
-#pragma unroll
-  for (int j = 0; j < 4; ++j) st_chunk(tile, f, p.nb, p.cb + j, v + 8 * j);
-}
-
 // Epilogue of one 128-feature half of a hidden layer for the thread's 32 rows.
 //   ENC: a pair's CGP columns are two endpoint units of CEP columns (D derivative columns each),
 //   otherwise one unit of CGP columns (2D derivative columns).
@@ -185,10 +188,10 @@ __device__ __forceinline__ void combine_unit(const float* u, const float* w, flo
 
 // Epilogue of encoder layer 5 (no activation) fused with the symmetric combine: reads the two endpoint
 // encodings of feature `lane`, writes smooth-max (feature lane) and smooth-min (feature 128+lane) with
-// their derivative columns, and pre-loads both into the skip accumulator.  y5 != nullptr: also writes the
-// encoder outputs (bias included) to the stash tile.
+// their derivative columns, and pre-loads both into the skip accumulator.  y5_addr != 0: also writes the
+// encoder outputs (bias included) to a 128-feature staging image in shared memory (training stash).
 template <class C>
-__device__ __forceinline__ void epi_combine(const EpiPos& p, int acc_col, int pre_col, float b, uint32_t act_addr, uint8_t* y5) {
+__device__ __forceinline__ void epi_combine(const EpiPos& p, int acc_col, int pre_col, float b, uint32_t act_addr, uint32_t y5_addr) {
   constexpr int CGP = C::CGP, CEP = C::CEP;
   float v[32], o[32];
   tmem_ld<32>(p.tmem + acc_col + 32 * p.rq, v);
@@ -197,7 +200,7 @@ __device__ __forceinline__ void epi_combine(const EpiPos& p, int acc_col, int pr
     v[u * CGP] += b;
     v[u * CGP + CEP] += b;
   }
-  if (y5 != nullptr) st_rows32_global(y5, p, p.lane, v);
+  if (y5_addr != 0) st_rows32(y5_addr, p, p.lane, v);
 #pragma unroll
   for (int u = 0; u < 32 / CGP; ++u) combine_unit<C, true>(v + u * CGP, v + u * CGP + CEP, o + u * CGP);
   st_rows32(act_addr, p, p.lane, o);
@@ -265,6 +268,8 @@ struct TcCtl {
   uint64_t full[S], empty[S];   // weight ring
   uint64_t xr[2];               // operand-tile half h complete (all epilogue threads arrive)
   uint64_t ar[2];               // accumulator half h complete (tcgen05.commit)
+  uint64_t sd[2][2];            // stash store of a buffer half h has finished reading shared memory; successive
+                                // events alternate between two barriers (a waiter may lag two events behind)
   uint32_t tmem_base;
 };
 
@@ -275,28 +280,33 @@ __device__ __forceinline__ void epi_publish(uint64_t* bar) {
   mbar_arrive(bar);
 }
 
-// MMA issue of one (contraction half kh, output half h) block: 2 stages x 4 UMMAs.
+// MMA issue of one (contraction half kh, output half h) block: 2 stages x 4 UMMAs.  Called by the whole
+// (converged) MMA warp; one elected lane issues.
 template <int S, class CTL>
 __device__ __forceinline__ void mma_block(CTL* ctl, uint32_t ring_addr, uint32_t opnd_addr, uint32_t d_tmem, int kh,
                                           bool accumulate_first, uint32_t& it) {
-  const uint32_t idesc = make_idesc(128, kRows, false, true);
+  constexpr uint32_t idesc = make_idesc(128, kRows, false, true);
+  constexpr uint32_t a_hi = desc_hi(1024), b_hi = desc_hi(kActSBO);
 #pragma unroll
   for (int s2 = 0; s2 < 2; ++s2) {
     const uint32_t slot = it % S, ph = (it / S) & 1;
-    mbar_wait(&ctl->full[slot], ph);
+    mbar_spin(&ctl->full[slot], ph);
     tc_fence_after();
+    if (elect_one()) {
+      const uint32_t a_lo = desc_lo(ring_addr + slot * kStageBytes, 16);
+      const uint32_t b_lo = desc_lo(opnd_addr + (kh * 2 + s2) * 8 * kActSBO, kActLBO);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint64_t ad = make_desc(ring_addr + slot * kStageBytes + j * 32, 16, 1024);
-      const uint64_t bd = make_desc(opnd_addr + ((kh * 2 + s2) * 4 + j) * 2 * kActSBO, kActLBO, kActSBO);
-      umma_f16(d_tmem, ad, bd, idesc, (accumulate_first || s2 > 0 || j > 0) ? 1u : 0u);
+      for (int j = 0; j < 4; ++j)
+        umma_f16_split(d_tmem, a_lo + 2 * j, a_hi, b_lo + j * ((2 * kActSBO) >> 4), b_hi, idesc,
+                       (accumulate_first || s2 > 0 || j > 0) ? 1u : 0u);
+      umma_commit(&ctl->empty[slot]);
     }
-    umma_commit(&ctl->empty[slot]);
+    __syncwarp();
     ++it;
   }
 }
 
-constexpr int kFwdRing = 8;                 // weight ring depth of the forward kernel
+constexpr int kFwdRing = 5;                 // weight ring depth of the forward kernel
 
 template <int D, int ORDER, bool TRAIN, int TAIL>
 __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdArgs a) {
@@ -306,8 +316,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
   constexpr int ACC_A = 0, ACC_B = 256;       // TMEM accumulator regions (columns)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* act = smem;
-  uint8_t* ring = smem + kTileBytes;
+  uint8_t* act = smem;                        // two operand-tile buffers: X_l in buffer l & 1
+  uint8_t* ring = smem + 2 * kTileBytes;
   __shared__ TcCtl<S> ctl;
   __shared__ TcTile<C> ts[2];
   __shared__ float y13s[2][kRows];
@@ -319,6 +329,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     mbar_init(&ctl.xr[1], kEpiThreads);
     mbar_init(&ctl.ar[0], 1);
     mbar_init(&ctl.ar[1], 1);
+    for (int i = 0; i < 4; ++i) mbar_init(&ctl.sd[i >> 1][i & 1], 1);
     fence_barrier_init();
   }
   if (warp == kMmaWarp) tmem_alloc(&ctl.tmem_base, 512);
@@ -343,43 +354,65 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
       }
     }
   } else if (warp == kMmaWarp) {
-    // ------------------------------------------------------------- MMA issuer
-    if (lane_id == 0) {
-      uint32_t it = 0, nx0 = 0, nx1 = 0;
-      const uint32_t ring_addr = smem_u32(ring), act_addr = smem_u32(act);
-      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    // ------------------------------------------------------------- MMA issuer (converged warp, elected lane issues)
+    uint32_t it = 0, nx0 = 0, nx1 = 0;
+    const uint32_t ring_addr = smem_u32(ring), act_addr = smem_u32(act);
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
 #pragma unroll 1
-        for (int l = 0; l < kNumLayers; ++l) {
-          const int K = c_K[l], KH = K >> 7, MH = halves(c_M[l]);
-          const bool skip = c_fwd_skip[l] != 0;   // accumulate onto the pre-loaded residual skip
-          const uint32_t acc = tmem_base + (skip ? ACC_B : ACC_A);
+      for (int l = 0; l < kNumLayers; ++l) {
+        const int K = c_K[l], KH = K >> 7, MH = halves(c_M[l]);
+        const bool skip = c_fwd_skip[l] != 0;   // accumulate onto the pre-loaded residual skip
+        const uint32_t acc = tmem_base + (skip ? ACC_B : ACC_A);
 #pragma unroll 1
-          for (int kh = 0; kh < KH; ++kh) {
-            if (kh == 0) { mbar_wait(&ctl.xr[0], nx0 & 1); ++nx0; }
-            else { mbar_wait(&ctl.xr[1], nx1 & 1); ++nx1; }
-            tc_fence_after();
-            if constexpr (TRAIN) {
-              bulk_s2g(a.st.X[l] + size_t(tile) * K * 256 + size_t(kh) * kHalfTileBytes, act + kh * kHalfTileBytes,
-                       kHalfTileBytes);
-              bulk_commit();
-            }
+        for (int kh = 0; kh < KH; ++kh) {
+          if (kh == 0) { mbar_spin(&ctl.xr[0], nx0 & 1); ++nx0; }
+          else { mbar_spin(&ctl.xr[1], nx1 & 1); ++nx1; }
+          tc_fence_after();
+          trace_evt(a.trace, lane_id == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x, 0, l, kh);   // operand half kh seen
 #pragma unroll 1
-            for (int h = 0; h < MH; ++h) {
-              mma_block<S>(&ctl, ring_addr, act_addr, acc + h * 128, kh, skip || kh > 0, it);
-              if (kh == KH - 1) {
-                // the epilogue of output half h overwrites features [128h, 128h+128) of the operand tile:
-                // the stash store of that half must have finished reading it
-                if constexpr (TRAIN) {
-                  if (h == 0 && MH == 2 && KH == 2) bulk_wait_read<1>();
-                  else bulk_wait_read<0>();
-                }
-                umma_commit(&ctl.ar[h]);
-              }
+          for (int h = 0; h < MH; ++h) {
+            mma_block<S>(&ctl, ring_addr, act_addr + (l & 1) * kTileBytes, acc + h * 128, kh, skip || kh > 0, it);
+            if (kh == KH - 1) {
+              if (elect_one()) umma_commit(&ctl.ar[h]);
+              __syncwarp();
+              trace_evt(a.trace, lane_id == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x, 0, l, 2 + h);   // commit of half h issued
             }
           }
         }
       }
-      if constexpr (TRAIN) bulk_wait0();
+    }
+  } else if (warp == kIoWarp) {
+    // ------------------------------------------------------------- training-stash stores
+    if constexpr (TRAIN) {
+      if (lane_id == 0) {
+        uint32_t nx0 = 0, nx1 = 0, ne[2] = {0, 0};
+        for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+#pragma unroll 1
+          for (int l = 0; l < kNumLayers; ++l) {
+            const int K = c_K[l], KH = K >> 7;
+#pragma unroll 1
+            for (int kh = 0; kh < KH; ++kh) {
+              if (kh == 0) { mbar_wait(&ctl.xr[0], nx0 & 1); ++nx0; }
+              else { mbar_wait(&ctl.xr[1], nx1 & 1); ++nx1; }
+              if (l == 6 && kh == 0) {
+                // encoder outputs Y5, staged by the combine epilogue in the upper half of buffer 1
+                bulk_s2g(a.st.Y5 + size_t(tile) * kHalfTileBytes, act + kTileBytes + kHalfTileBytes, kHalfTileBytes);
+                bulk_commit();
+                bulk_wait_read<0>();
+                mbar_arrive(&ctl.sd[1][ne[1] & 1]);
+                ++ne[1];
+              }
+              bulk_s2g(a.st.X[l] + size_t(tile) * K * 256 + size_t(kh) * kHalfTileBytes,
+                       act + (l & 1) * kTileBytes + kh * kHalfTileBytes, kHalfTileBytes);
+              bulk_commit();
+              bulk_wait_read<0>();
+              mbar_arrive(&ctl.sd[kh][ne[kh] & 1]);    // this half of the buffer may be overwritten (by the epilogue of layer l+1)
+              ++ne[kh];
+            }
+          }
+        }
+        bulk_wait0();
+      }
     }
   } else {
     // ------------------------------------------------------------- epilogue warps
@@ -403,64 +436,93 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     }
     named_bar_sync(1, kEpiThreads);
     int par = 0;
-#define PNTF_WAIT_ACC0() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); }
-#define PNTF_WAIT_ACC1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); }
+    uint32_t nsd0 = 0, nsd1 = 0;
+    const uint32_t buf0 = act_addr, buf1 = act_addr + kTileBytes;
+    // TRAIN: before a buffer half is overwritten the stash store of its previous occupant (the operand tile of two
+    // layers earlier) must have finished reading it; sd[h] completions are consumed strictly in order.
+#define PNTF_WAIT_SD0() { if constexpr (TRAIN) { mbar_wait(&ctl.sd[0][nsd0 & 1], (nsd0 >> 1) & 1); ++nsd0; } }
+#define PNTF_WAIT_SD1() { if constexpr (TRAIN) { mbar_wait(&ctl.sd[1][nsd1 & 1], (nsd1 >> 1) & 1); ++nsd1; } }
+#define PNTF_WAIT_ACC0() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); ++tl; trace_evt(a.trace, tron, trole, tl, 0); }
+#define PNTF_WAIT_ACC1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); trace_evt(a.trace, tron, trole, tl, 2); }
+#define PNTF_PUB(h) { epi_publish(&ctl.xr[h]); trace_evt(a.trace, tron, trole, tl < 0 ? 15 : tl, 1 + 2 * (h)); }
+    const int trole = (tid == 0) ? 1 : 2;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
       const int64_t pair0 = a.pair_begin + tile * P;
-      fourier_tile<C>(a, ts[par], act_addr);
-      epi_publish(&ctl.xr[0]);
-      epi_publish(&ctl.xr[1]);
+      const bool first = tile == int64_t(blockIdx.x);
+      int tl = -1;
+      const bool tron = (tid == 0 || tid == kEpiThreads - 1) && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x;
+      if (!first) {   // buffer 0 was last occupied by X12 of the previous tile (sd[1] also delivers X11's second half)
+        PNTF_WAIT_SD0();
+        PNTF_WAIT_SD1();
+        PNTF_WAIT_SD1();
+      }
+      fourier_tile<C>(a, ts[par], buf0);
+      PNTF_PUB(0);
+      PNTF_PUB(1);
       // encoder: L0 ; {L1, L2(+skip)} ; {L3, L4(+skip)} ; L5 + combine
       PNTF_WAIT_ACC0();
-      epi_hidden_half<C, true, true>(p, ACC_A, ACC_B, p.lane, __ldg(prm + c_b[0] + p.lane), act_addr, compat);
-      epi_publish(&ctl.xr[0]);
+      if (!first) PNTF_WAIT_SD0();    // X13 of the previous tile
+      epi_hidden_half<C, true, true>(p, ACC_A, ACC_B, p.lane, __ldg(prm + c_b[0] + p.lane), buf1, compat);
+      PNTF_PUB(0);
       PNTF_WAIT_ACC0();
-      epi_hidden_half<C, true, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[1] + p.lane), act_addr, false);
-      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT_SD0();
+      epi_hidden_half<C, true, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[1] + p.lane), buf0, false);
+      PNTF_PUB(0);
       PNTF_WAIT_ACC0();
-      epi_hidden_half<C, true, true>(p, ACC_B, ACC_B, p.lane, __ldg(prm + c_b[2] + p.lane), act_addr, false);
-      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT_SD0();
+      epi_hidden_half<C, true, true>(p, ACC_B, ACC_B, p.lane, __ldg(prm + c_b[2] + p.lane), buf1, false);
+      PNTF_PUB(0);
       PNTF_WAIT_ACC0();
-      epi_hidden_half<C, true, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[3] + p.lane), act_addr, false);
-      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT_SD0();
+      epi_hidden_half<C, true, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[3] + p.lane), buf0, false);
+      PNTF_PUB(0);
       PNTF_WAIT_ACC0();
-      epi_hidden_half<C, true, false>(p, ACC_B, 0, p.lane, __ldg(prm + c_b[4] + p.lane), act_addr, false);
-      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT_SD0();
+      epi_hidden_half<C, true, false>(p, ACC_B, 0, p.lane, __ldg(prm + c_b[4] + p.lane), buf1, false);
+      PNTF_PUB(0);
       PNTF_WAIT_ACC0();
-      epi_combine<C>(p, ACC_A, ACC_B, __ldg(prm + c_b[5] + p.lane), act_addr,
-                     TRAIN ? a.st.Y5 + size_t(tile) * kHalfTileBytes : nullptr);
-      epi_publish(&ctl.xr[0]);
-      epi_publish(&ctl.xr[1]);
+      PNTF_WAIT_SD0();
+      PNTF_WAIT_SD1();                // X0's second half (buffer 0)
+      epi_combine<C>(p, ACC_A, ACC_B, __ldg(prm + c_b[5] + p.lane), buf0, TRAIN ? buf1 + kHalfTileBytes : 0u);
+      PNTF_PUB(0);
+      PNTF_PUB(1);
       // generator: 3 x {La, Lb(+skip)} ; L12 ; L13
 #pragma unroll 1
       for (int ii = 0; ii < 3; ++ii) {
         const float* ba = prm + c_b[6 + 2 * ii] + p.lane;
         const float* bb = prm + c_b[7 + 2 * ii] + p.lane;
         PNTF_WAIT_ACC0();
-        epi_hidden_half<C, false, false>(p, ACC_A, 0, p.lane, __ldg(ba), act_addr, false);
-        epi_publish(&ctl.xr[0]);
+        PNTF_WAIT_SD0();
+        epi_hidden_half<C, false, false>(p, ACC_A, 0, p.lane, __ldg(ba), buf1, false);
+        PNTF_PUB(0);
         PNTF_WAIT_ACC1();
-        epi_hidden_half<C, false, false>(p, ACC_A + 128, 0, 128 + p.lane, __ldg(ba + 128), act_addr, false);
-        epi_publish(&ctl.xr[1]);
+        PNTF_WAIT_SD1();              // ii = 0: the Y5 staging image
+        epi_hidden_half<C, false, false>(p, ACC_A + 128, 0, 128 + p.lane, __ldg(ba + 128), buf1, false);
+        PNTF_PUB(1);
         if (ii < 2) {
           PNTF_WAIT_ACC0();
-          epi_hidden_half<C, false, true>(p, ACC_B, ACC_B, p.lane, __ldg(bb), act_addr, false);
-          epi_publish(&ctl.xr[0]);
+          PNTF_WAIT_SD0();
+          epi_hidden_half<C, false, true>(p, ACC_B, ACC_B, p.lane, __ldg(bb), buf0, false);
+          PNTF_PUB(0);
           PNTF_WAIT_ACC1();
-          epi_hidden_half<C, false, true>(p, ACC_B + 128, ACC_B + 128, 128 + p.lane, __ldg(bb + 128), act_addr, false);
-          epi_publish(&ctl.xr[1]);
+          PNTF_WAIT_SD1();
+          epi_hidden_half<C, false, true>(p, ACC_B + 128, ACC_B + 128, 128 + p.lane, __ldg(bb + 128), buf0, false);
+          PNTF_PUB(1);
         } else {
           PNTF_WAIT_ACC0();
-          epi_hidden_half<C, false, false>(p, ACC_B, 0, p.lane, __ldg(bb), act_addr, false);
-          epi_publish(&ctl.xr[0]);
+          PNTF_WAIT_SD0();
+          epi_hidden_half<C, false, false>(p, ACC_B, 0, p.lane, __ldg(bb), buf0, false);
+          PNTF_PUB(0);
           PNTF_WAIT_ACC1();
-          epi_hidden_half<C, false, false>(p, ACC_B + 128, 0, 128 + p.lane, __ldg(bb + 128), act_addr, false);
-          epi_publish(&ctl.xr[1]);
+          PNTF_WAIT_SD1();
+          epi_hidden_half<C, false, false>(p, ACC_B + 128, 0, 128 + p.lane, __ldg(bb + 128), buf0, false);
+          PNTF_PUB(1);
         }
       }
       PNTF_WAIT_ACC0();
-      epi_hidden_half<C, false, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[12] + p.lane), act_addr, false);
-      epi_publish(&ctl.xr[0]);
+      PNTF_WAIT_SD0();
+      epi_hidden_half<C, false, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[12] + p.lane), buf1, false);
+      PNTF_PUB(0);
       PNTF_WAIT_ACC0();
       // output layer: lane 0 of the accumulator holds y13 for all rows
       if ((warp & 3) == 0) {
@@ -527,6 +589,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     }
 #undef PNTF_WAIT_ACC0
 #undef PNTF_WAIT_ACC1
+#undef PNTF_WAIT_SD0
+#undef PNTF_WAIT_SD1
+#undef PNTF_PUB
   }
   tc_fence_before();
   __syncthreads();

@@ -43,8 +43,8 @@ constexpr int kTileBytes = 256 * kRows * 2; // activation tile: 256 features x 1
 constexpr int kHalfTileBytes = kTileBytes / 2;
 constexpr int kEpiWarps = 16;
 constexpr int kEpiThreads = kEpiWarps * 32; // epilogue warps 0..15: lane quarter = warp % 4, row quarter = warp / 4
-constexpr int kTcThreads = kEpiThreads + 64;   // + producer warp 16 + MMA warp 17
-constexpr int kProducerWarp = kEpiWarps, kMmaWarp = kEpiWarps + 1;
+constexpr int kTcThreads = kEpiThreads + 96;   // + producer warp 16 + MMA warp 17 + stash I/O warp 18
+constexpr int kProducerWarp = kEpiWarps, kMmaWarp = kEpiWarps + 1, kIoWarp = kEpiWarps + 2;
 
 // per-layer run-time tables (constant memory: indexed with a run-time layer number by the issuer threads)
 static __constant__ int c_K[kNumLayers] = {256, 128, 128, 128, 128, 128, 256, 256, 256, 256, 256, 256, 256, 128};

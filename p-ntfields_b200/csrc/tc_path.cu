@@ -1,5 +1,8 @@
 // Host side of the tensor-core precision mode (PNTF_PREC_TC): workspace carving and launches of the
 // tcgen05 kernels.  Called from the C-ABI entry points in capi.cu.
+#include <cstdio>
+#include <cstdlib>
+
 #include "../../include/pntf_b200.h"
 #include "tc_api.cuh"
 #include "tc_dw.cuh"
@@ -27,12 +30,46 @@ static int tc_pack(const float* params, uint8_t* fwd_img, uint8_t* rev_img, cuda
   return launch_check("tc_pack_images");
 }
 
-constexpr size_t kFwdSmem = size_t(kTileBytes) + size_t(kFwdRing) * kStageBytes + 1024;
+constexpr size_t kFwdSmem = 2 * size_t(kTileBytes) + size_t(kFwdRing) * kStageBytes + 1024;
 constexpr size_t kRevSmem = 2 * size_t(kTileBytes) + size_t(kRevRing) * kStageBytes + (kNumBiasSlots + 132) * sizeof(float) + 1024;
 
+// Debug aid (PNTF_TRACE=1 in the environment): the forward kernel records clock64 time stamps of the
+// hand-over events of CTA 0's third tile; they are printed to stderr after a stream synchronisation.
+// Never active in normal runs (allocates and synchronises).
+static long long* trace_begin() {
+  static const bool on = getenv("PNTF_TRACE") != nullptr;
+  if (!on) return nullptr;
+  long long* buf = nullptr;
+  if (cudaMalloc(&buf, 3 * 16 * 4 * sizeof(long long)) != cudaSuccess) return nullptr;
+  cudaMemset(buf, 0, 3 * 16 * 4 * sizeof(long long));
+  return buf;
+}
+static void trace_end(long long* buf, cudaStream_t s, const char* what) {
+  if (buf == nullptr) return;
+  long long h[3 * 16 * 4];
+  cudaStreamSynchronize(s);
+  cudaMemcpy(h, buf, sizeof(h), cudaMemcpyDeviceToHost);
+  cudaFree(buf);
+  long long t0 = 0;
+  for (int i = 0; i < 3 * 16 * 4; ++i)
+    if (h[i] != 0 && (t0 == 0 || h[i] < t0)) t0 = h[i];
+  fprintf(stderr, "PNTF_TRACE %s (cycles since first event; role 0 = MMA issuer: operand half 0/1 seen, commit half 0/1 issued; "
+                  "role 1/2 = epilogue thread 0 / last: acc half 0 ready, half 0 published, acc half 1 ready, half 1 published)\n", what);
+  for (int role = 0; role < 3; ++role)
+    for (int l = 0; l < 16; ++l) {
+      const long long* e = h + (role * 16 + l) * 4;
+      if (e[0] == 0 && e[1] == 0 && e[2] == 0 && e[3] == 0) continue;
+      fprintf(stderr, "  role %d layer %2d :", role, l);
+      for (int k = 0; k < 4; ++k) fprintf(stderr, " %8lld", e[k] ? e[k] - t0 : -1LL);
+      fprintf(stderr, "\n");
+    }
+}
+
 template <int D, int ORDER, bool TRAIN, int TAIL>
-static int tc_launch_forward(const TcFwdArgs& a, cudaStream_t s) {
+static int tc_launch_forward(const TcFwdArgs& a_in, cudaStream_t s) {
   using C = TcCfg<D, ORDER>;
+  TcFwdArgs a = a_in;
+  a.trace = trace_begin();
   auto k = tc_forward_kernel<D, ORDER, TRAIN, TAIL>;
   const size_t smem = kFwdSmem;
   if (int rc = tc_set_smem(k, smem)) return rc;
@@ -41,6 +78,7 @@ static int tc_launch_forward(const TcFwdArgs& a, cudaStream_t s) {
   prof_start(KC_TC_FORWARD, s);
   k<<<grid, kTcThreads, smem, s>>>(a);
   prof_stop(s);
+  trace_end(a.trace, s, "tc_forward");
   return launch_check("tc_forward");
 }
 
@@ -128,9 +166,12 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     tc_carve_stash(a.st, stash, size_t(tiles));
     r.rimg = rimg; r.grad = grad_params; r.out_scale = out_scale;
     const int grid = int(tiles < sm_count() ? tiles : sm_count());
+    a.trace = (t0 == 0) ? trace_begin() : nullptr;
     prof_start(KC_TC_FORWARD, s);
     kf<<<grid, kTcThreads, smem_f, s>>>(a);
     prof_stop(s);
+    trace_end(a.trace, s, "tc_forward(train)");
+    a.trace = nullptr;
     if (int rc = launch_check("tc_forward(train)")) return rc;
     prof_start(KC_TC_REVERSE, s);
     kr<<<grid, kTcThreads, smem_r, s>>>(r);

@@ -166,6 +166,7 @@ struct TcRevCtl {
   uint64_t xr[2];     // Ybar operand-tile half complete (= stash-buffer half consumed)
   uint64_t ar[2];     // product half complete (= operand-tile half free again)
   uint64_t yb[2];     // stash-buffer half loaded
+  uint64_t sd[2];     // stash store of operand-tile half h has finished reading shared memory
   uint32_t tmem_base;
 };
 
@@ -197,6 +198,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
       mbar_init(&ctl.xr[h], kEpiThreads);
       mbar_init(&ctl.ar[h], 1);
       mbar_init(&ctl.yb[h], 1);
+      mbar_init(&ctl.sd[h], 1);
     }
     fence_barrier_init();
   }
@@ -221,9 +223,47 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
       }
     }
   } else if (warp == kMmaWarp) {
+    // converged warp, elected lane issues
+    uint32_t it = 0, nx0 = 0, nx1 = 0;
+    const uint32_t ring_addr = smem_u32(ring), gt_addr = smem_u32(gt);
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+#pragma unroll 1
+      for (int l = 12; l >= 1; --l) {
+        const int MH = halves(c_M[l]), OH = c_K[l] >> 7;
+        const bool skip = c_rev_skip[l] != 0;
+        const uint32_t acc = tmem_base + (c_rev_acc[l] ? ACC_B : ACC_A);
+#pragma unroll 1
+        for (int kh = 0; kh < MH; ++kh) {
+          if (kh == 0) { mbar_spin(&ctl.xr[0], nx0 & 1); ++nx0; }
+          else { mbar_spin(&ctl.xr[1], nx1 & 1); ++nx1; }
+          tc_fence_after();
+#pragma unroll 1
+          for (int h = 0; h < OH; ++h) {
+            mma_block<S>(&ctl, ring_addr, gt_addr, acc + h * 128, kh, skip || kh > 0, it);
+            if (kh == MH - 1) {
+              if (elect_one()) {
+                if (MH == 1 && OH == 2) {
+                  // both output halves contract over operand half 0: release it after the last block only
+                  if (h == 1) {
+                    umma_commit(&ctl.ar[0]);
+                    umma_commit(&ctl.ar[1]);
+                  }
+                } else {
+                  umma_commit(&ctl.ar[h]);
+                }
+              }
+              __syncwarp();
+            }
+          }
+        }
+      }
+      mbar_spin(&ctl.xr[0], nx0 & 1);   // step 0 has no product
+      ++nx0;
+    }
+  } else if (warp == kIoWarp) {
+    // ------------------------------------------------------------- stash I/O: Ybar stores, prefetch of the forward outputs
     if (lane_id == 0) {
-      uint32_t it = 0, nx0 = 0, nx1 = 0;
-      const uint32_t ring_addr = smem_u32(ring), gt_addr = smem_u32(gt);
+      uint32_t nx0 = 0, nx1 = 0;
       // stash source of step l: the forward outputs X_{l+1} (Y5 for the combine step)
       auto src = [&](int l, int64_t tile) -> const uint8_t* {
         return (l == 5) ? a.st.Y5 + size_t(tile) * kHalfTileBytes
@@ -233,14 +273,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
         mbar_arrive_expect_tx(&ctl.yb[h], kHalfTileBytes);
         bulk_g2s(xbuf + h * kHalfTileBytes, src(l, tile) + size_t(h) * kHalfTileBytes, kHalfTileBytes, &ctl.yb[h]);
       };
-      mbar_arrive(&ctl.ar[0]);     // completion #0: the operand tile starts out free
       if (int64_t(blockIdx.x) < ntiles) load_half(12, blockIdx.x, 0);
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
 #pragma unroll 1
         for (int l = 12; l >= 0; --l) {
-          const int M = c_M[l], MH = halves(M), OH = c_K[l] >> 7;
-          const bool skip = c_rev_skip[l] != 0;
-          const uint32_t acc = tmem_base + (c_rev_acc[l] ? ACC_B : ACC_A);
+          const int M = c_M[l], MH = halves(M);
           const int ln = (l > 0) ? l - 1 : 12;
           const int64_t tn = (l > 0) ? tile : tile + gridDim.x;
           const int MHn = (ln == 5) ? 1 : halves(c_M[ln]);
@@ -248,40 +285,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
           for (int kh = 0; kh < MH; ++kh) {
             if (kh == 0) { mbar_wait(&ctl.xr[0], nx0 & 1); ++nx0; }
             else { mbar_wait(&ctl.xr[1], nx1 & 1); ++nx1; }
-            tc_fence_after();
-            bulk_s2g(a.st.G[l] + size_t(tile) * M * 256 + size_t(kh) * kHalfTileBytes, gt + kh * kHalfTileBytes,
-                     kHalfTileBytes);
-            bulk_commit();
-            // the epilogue is done with stash-buffer half kh: fetch the next step's half
+            // the epilogue is done with stash-buffer half kh: fetch the next step's half first (critical path)
             if (tn < ntiles) {
               if (kh < MHn) load_half(ln, tn, kh);
               if (kh == MH - 1)
                 for (int hh = MH; hh < MHn; ++hh) load_half(ln, tn, hh);
             }
-            if (l >= 1) {
-#pragma unroll 1
-              for (int h = 0; h < OH; ++h) {
-                mma_block<S>(&ctl, ring_addr, gt_addr, acc + h * 128, kh, skip || kh > 0, it);
-                if (kh == MH - 1) {
-                  // the next epilogue overwrites operand-tile half h: its stash store must have read it
-                  if (MH == 1 && OH == 2) {
-                    // both output halves contract over operand half 0: release it after the last block only
-                    if (h == 1) {
-                      bulk_wait_read<0>();
-                      umma_commit(&ctl.ar[0]);
-                      umma_commit(&ctl.ar[1]);
-                    }
-                  } else {
-                    if (h == 0 && MH == 2) bulk_wait_read<1>();
-                    else bulk_wait_read<0>();
-                    umma_commit(&ctl.ar[h]);
-                  }
-                }
-              }
-            } else {
-              bulk_wait_read<0>();
-              mbar_arrive(&ctl.ar[0]);
-            }
+            bulk_s2g(a.st.G[l] + size_t(tile) * M * 256 + size_t(kh) * kHalfTileBytes, gt + kh * kHalfTileBytes,
+                     kHalfTileBytes);
+            bulk_commit();
+            bulk_wait_read<0>();
+            mbar_arrive(&ctl.sd[kh]);    // the next epilogue may overwrite this half of the operand tile
           }
         }
       }
@@ -293,7 +307,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
     const float* prm = a.params;
     const float w13f = __ldg(prm + c_w[13] + p.lane);
     float dw13 = 0.f, unused = 0.f;
-    uint32_t nar0 = 0, nar1 = 0, ny0 = 0, ny1 = 0;
+    uint32_t nar0 = 0, nar1 = 0, ny0 = 0, ny1 = 0, nsd0 = 0, nsd1 = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int64_t pair0 = a.pair_begin + tile * P;
       // ---- loss seeds and output-activation adjoint (one thread per pair), S:890-936 / M:914-951
@@ -337,11 +351,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
         for (int c = 0; c < CGP; ++c) g13s[tid * CGP + c] = gy[c];
       }
       named_bar_sync(1, kEpiThreads);
-#define PNTF_WAIT0() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; }
-#define PNTF_WAIT1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); mbar_wait(&ctl.yb[1], ny1 & 1); ++ny1; }
+      // product half ready (adjoint input, and the product is done reading operand-tile half h), the stash store of
+      // that operand-tile half is done, and the stashed forward outputs of this step are loaded
+#define PNTF_WAIT_SD0() { mbar_wait(&ctl.sd[0], nsd0 & 1); ++nsd0; }
+#define PNTF_WAIT_SD1() { mbar_wait(&ctl.sd[1], nsd1 & 1); ++nsd1; }
+#define PNTF_WAIT0() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); PNTF_WAIT_SD0(); mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; }
+      // (operand-tile half 1 was last stored by step l+1, or for l = 11 by step 6 of the previous tile)
+#define PNTF_WAIT1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); if (l != 11 || tile != int64_t(blockIdx.x)) PNTF_WAIT_SD1(); mbar_wait(&ctl.yb[1], ny1 & 1); ++ny1; }
 #define PNTF_DB(l, h, v) atomicAdd(sdb + c_db[l] + (h) * 128 + p.lane, (v))
-      // ---- generator
-      PNTF_WAIT0();
+      // ---- generator (step 12 has no accumulator input; the operand tile was last stored by step 0 of the previous tile)
+      if (tile != int64_t(blockIdx.x)) PNTF_WAIT_SD0();
+      { mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; }
       PNTF_DB(12, 0, (epi_adjoint_half<C, false, false, true>(p, 0, 0, p.lane, x_addr, gt_addr, g13s, w13f, dw13)));
       epi_publish(&ctl.xr[0]);
 #pragma unroll 1
