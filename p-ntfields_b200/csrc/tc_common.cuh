@@ -234,6 +234,10 @@ template <> __device__ __forceinline__ void tmem_st<32>(uint32_t taddr, const fl
   asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr), "r"(__float_as_uint(v[0])),"r"(__float_as_uint(v[1])),"r"(__float_as_uint(v[2])),"r"(__float_as_uint(v[3])),"r"(__float_as_uint(v[4])),"r"(__float_as_uint(v[5])),"r"(__float_as_uint(v[6])),"r"(__float_as_uint(v[7])),"r"(__float_as_uint(v[8])),"r"(__float_as_uint(v[9])),"r"(__float_as_uint(v[10])),"r"(__float_as_uint(v[11])),"r"(__float_as_uint(v[12])),"r"(__float_as_uint(v[13])),"r"(__float_as_uint(v[14])),"r"(__float_as_uint(v[15])),"r"(__float_as_uint(v[16])),"r"(__float_as_uint(v[17])),"r"(__float_as_uint(v[18])),"r"(__float_as_uint(v[19])),"r"(__float_as_uint(v[20])),"r"(__float_as_uint(v[21])),"r"(__float_as_uint(v[22])),"r"(__float_as_uint(v[23])),"r"(__float_as_uint(v[24])),"r"(__float_as_uint(v[25])),"r"(__float_as_uint(v[26])),"r"(__float_as_uint(v[27])),"r"(__float_as_uint(v[28])),"r"(__float_as_uint(v[29])),"r"(__float_as_uint(v[30])),"r"(__float_as_uint(v[31]))
                : "memory");
 }
+// fire-and-forget fp32 add to a shared-memory word (shared-window address)
+__device__ __forceinline__ void red_shared_add(uint32_t addr, float v) {
+  asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
 // barrier among a subset of the CTA's warps (id 1..15)
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
 

@@ -173,9 +173,12 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     trace_end(a.trace, s, "tc_forward(train)");
     a.trace = nullptr;
     if (int rc = launch_check("tc_forward(train)")) return rc;
+    a.trace = (t0 == 0) ? trace_begin() : nullptr;
     prof_start(KC_TC_REVERSE, s);
     kr<<<grid, kTcThreads, smem_r, s>>>(r);
     prof_stop(s);
+    trace_end(a.trace, s, "tc_reverse (role 1: acc half 0 ready, stash inputs ready, half 0 published, half 1 published)");
+    a.trace = nullptr;
     if (int rc = launch_check("tc_reverse")) return rc;
     TcDwArgs dw{};
     dw.st = a.st; dw.units = units; dw.ntiles = tiles; dw.grad = grad_params; dw.out_scale = out_scale;

@@ -237,9 +237,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
           if (kh == 0) { mbar_spin(&ctl.xr[0], nx0 & 1); ++nx0; }
           else { mbar_spin(&ctl.xr[1], nx1 & 1); ++nx1; }
           tc_fence_after();
+          trace_evt(a.trace, lane_id == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x, 0, l, kh);
 #pragma unroll 1
           for (int h = 0; h < OH; ++h) {
             mma_block<S>(&ctl, ring_addr, gt_addr, acc + h * 128, kh, skip || kh > 0, it);
+            if (kh == MH - 1) trace_evt(a.trace, lane_id == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x, 0, l, 2 + h);
             if (kh == MH - 1) {
               if (elect_one()) {
                 if (MH == 1 && OH == 2) {
@@ -269,28 +271,32 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
         return (l == 5) ? a.st.Y5 + size_t(tile) * kHalfTileBytes
                         : a.st.X[l + 1] + size_t(tile) * size_t(c_K[l + 1]) * 256;
       };
-      auto load_half = [&](int l, int64_t tile, int h) {
-        mbar_arrive_expect_tx(&ctl.yb[h], kHalfTileBytes);
-        bulk_g2s(xbuf + h * kHalfTileBytes, src(l, tile) + size_t(h) * kHalfTileBytes, kHalfTileBytes, &ctl.yb[h]);
+      // Stash-buffer halves: step 12 and the generator steps use half h for features [128h, 128h+128); the
+      // 128-feature encoder steps alternate (5 -> half 0, 4 -> 1, 3 -> 0, 2 -> 1, 1 -> 0, 0 -> 1) so that their
+      // inputs can be fetched two steps ahead.  `load(l, tile, src_half, buf_half)`.
+      auto load = [&](int l, int64_t tile, int sh, int bh) {
+        if (tile >= ntiles) return;
+        mbar_arrive_expect_tx(&ctl.yb[bh], kHalfTileBytes);
+        bulk_g2s(xbuf + bh * kHalfTileBytes, src(l, tile) + size_t(sh) * kHalfTileBytes, kHalfTileBytes, &ctl.yb[bh]);
       };
-      if (int64_t(blockIdx.x) < ntiles) load_half(12, blockIdx.x, 0);
+      load(12, blockIdx.x, 0, 0);
+      load(11, blockIdx.x, 1, 1);
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int64_t tn = tile + gridDim.x;
 #pragma unroll 1
         for (int l = 12; l >= 0; --l) {
           const int M = c_M[l], MH = halves(M);
-          const int ln = (l > 0) ? l - 1 : 12;
-          const int64_t tn = (l > 0) ? tile : tile + gridDim.x;
-          const int MHn = (ln == 5) ? 1 : halves(c_M[ln]);
 #pragma unroll 1
           for (int kh = 0; kh < MH; ++kh) {
             if (kh == 0) { mbar_wait(&ctl.xr[0], nx0 & 1); ++nx0; }
             else { mbar_wait(&ctl.xr[1], nx1 & 1); ++nx1; }
-            // the epilogue is done with stash-buffer half kh: fetch the next step's half first (critical path)
-            if (tn < ntiles) {
-              if (kh < MHn) load_half(ln, tn, kh);
-              if (kh == MH - 1)
-                for (int hh = MH; hh < MHn; ++hh) load_half(ln, tn, hh);
-            }
+            // the epilogue is done with a stash-buffer half: refill it first (critical path), then store Ybar
+            if (l == 12) load(11, tile, 0, 0);
+            else if (l >= 7) load(l - 1, tile, kh, kh);
+            else if (l == 6) { if (kh == 0) load(5, tile, 0, 0); else load(4, tile, 0, 1); }
+            else if (l >= 2) load(l - 2, tile, 0, (l + 1) & 1);
+            else if (l == 1) load(12, tn, 0, 0);
+            else load(11, tn, 1, 1);
             bulk_s2g(a.st.G[l] + size_t(tile) * M * 256 + size_t(kh) * kHalfTileBytes, gt + kh * kHalfTileBytes,
                      kHalfTileBytes);
             bulk_commit();
@@ -303,13 +309,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
     }
   } else {
     const EpiPos p = epi_pos(tmem_base);
-    const uint32_t gt_addr = smem_u32(gt), x_addr = smem_u32(xbuf);
+    const uint32_t gt_addr = smem_u32(gt), x_addr = smem_u32(xbuf), sdb_addr = smem_u32(sdb);
     const float* prm = a.params;
     const float w13f = __ldg(prm + c_w[13] + p.lane);
     float dw13 = 0.f, unused = 0.f;
     uint32_t nar0 = 0, nar1 = 0, ny0 = 0, ny1 = 0, nsd0 = 0, nsd1 = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int64_t pair0 = a.pair_begin + tile * P;
+      int tl = 12;
+      const bool tron = tid == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x;
       // ---- loss seeds and output-activation adjoint (one thread per pair), S:890-936 / M:914-951
       if (tid < P) {
         const int64_t pair = pair0 + tid;
@@ -355,57 +363,59 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
       // that operand-tile half is done, and the stashed forward outputs of this step are loaded
 #define PNTF_WAIT_SD0() { mbar_wait(&ctl.sd[0], nsd0 & 1); ++nsd0; }
 #define PNTF_WAIT_SD1() { mbar_wait(&ctl.sd[1], nsd1 & 1); ++nsd1; }
-#define PNTF_WAIT0() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); PNTF_WAIT_SD0(); mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; }
+#define PNTF_WAIT0_Y1() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); --tl; trace_evt(a.trace, tron, 1, tl, 0); PNTF_WAIT_SD0(); mbar_wait(&ctl.yb[1], ny1 & 1); ++ny1; trace_evt(a.trace, tron, 1, tl, 1); }
+#define PNTF_WAIT0() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); --tl; trace_evt(a.trace, tron, 1, tl, 0); PNTF_WAIT_SD0(); mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; trace_evt(a.trace, tron, 1, tl, 1); }
       // (operand-tile half 1 was last stored by step l+1, or for l = 11 by step 6 of the previous tile)
 #define PNTF_WAIT1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); if (l != 11 || tile != int64_t(blockIdx.x)) PNTF_WAIT_SD1(); mbar_wait(&ctl.yb[1], ny1 & 1); ++ny1; }
-#define PNTF_DB(l, h, v) atomicAdd(sdb + c_db[l] + (h) * 128 + p.lane, (v))
+#define PNTF_DB(l, h, v) red_shared_add(sdb_addr + 4u * uint32_t(c_db[l] + (h) * 128 + p.lane), (v))
       // ---- generator (step 12 has no accumulator input; the operand tile was last stored by step 0 of the previous tile)
       if (tile != int64_t(blockIdx.x)) PNTF_WAIT_SD0();
-      { mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; }
+      { mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; trace_evt(a.trace, tron, 1, 12, 1); }
       PNTF_DB(12, 0, (epi_adjoint_half<C, false, false, true>(p, 0, 0, p.lane, x_addr, gt_addr, g13s, w13f, dw13)));
-      epi_publish(&ctl.xr[0]);
+      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
 #pragma unroll 1
       for (int l = 11; l >= 6; --l) {
         const bool second = (l & 1) != 0;      // second layer of a block: reads B, pre-loads the skip adjoint in place
         if (second) {
           PNTF_WAIT0();
           PNTF_DB(l, 0, (epi_adjoint_half<C, false, true, false>(p, ACC_B, ACC_B, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
-          epi_publish(&ctl.xr[0]);
+          { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
           PNTF_WAIT1();
           PNTF_DB(l, 1, (epi_adjoint_half<C, false, true, false>(p, ACC_B + 128, ACC_B + 128, 128 + p.lane, x_addr, gt_addr,
                                                                   nullptr, 0.f, unused)));
-          epi_publish(&ctl.xr[1]);
+          { epi_publish(&ctl.xr[1]); trace_evt(a.trace, tron, 1, tl, 3); }
         } else {
           PNTF_WAIT0();
           PNTF_DB(l, 0, (epi_adjoint_half<C, false, false, false>(p, ACC_A, 0, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
-          epi_publish(&ctl.xr[0]);
+          { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
           PNTF_WAIT1();
           PNTF_DB(l, 1, (epi_adjoint_half<C, false, false, false>(p, ACC_A + 128, 0, 128 + p.lane, x_addr, gt_addr, nullptr,
                                                                    0.f, unused)));
-          epi_publish(&ctl.xr[1]);
+          { epi_publish(&ctl.xr[1]); trace_evt(a.trace, tron, 1, tl, 3); }
         }
       }
       // ---- combine (needs both halves of the adjoint of its output) and encoder
       PNTF_WAIT0();
       { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); }
       PNTF_DB(5, 0, epi_combine_adjoint<C>(p, ACC_B, x_addr, gt_addr));
-      epi_publish(&ctl.xr[0]);
-      PNTF_WAIT0();
-      PNTF_DB(4, 0, (epi_adjoint_half<C, true, true, false>(p, ACC_A, ACC_B, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
-      epi_publish(&ctl.xr[0]);
+      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+      PNTF_WAIT0_Y1();
+      PNTF_DB(4, 0, (epi_adjoint_half<C, true, true, false>(p, ACC_A, ACC_B, p.lane, x_addr + kHalfTileBytes, gt_addr, nullptr, 0.f, unused)));
+      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
       PNTF_WAIT0();
       PNTF_DB(3, 0, (epi_adjoint_half<C, true, false, false>(p, ACC_A, 0, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
-      epi_publish(&ctl.xr[0]);
-      PNTF_WAIT0();
-      PNTF_DB(2, 0, (epi_adjoint_half<C, true, true, false>(p, ACC_B, ACC_B, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
-      epi_publish(&ctl.xr[0]);
+      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+      PNTF_WAIT0_Y1();
+      PNTF_DB(2, 0, (epi_adjoint_half<C, true, true, false>(p, ACC_B, ACC_B, p.lane, x_addr + kHalfTileBytes, gt_addr, nullptr, 0.f, unused)));
+      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
       PNTF_WAIT0();
       PNTF_DB(1, 0, (epi_adjoint_half<C, true, false, false>(p, ACC_A, 0, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
-      epi_publish(&ctl.xr[0]);
-      PNTF_WAIT0();
-      PNTF_DB(0, 0, (epi_adjoint_half<C, true, false, false>(p, ACC_B, 0, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
-      epi_publish(&ctl.xr[0]);
+      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+      PNTF_WAIT0_Y1();
+      PNTF_DB(0, 0, (epi_adjoint_half<C, true, false, false>(p, ACC_B, 0, p.lane, x_addr + kHalfTileBytes, gt_addr, nullptr, 0.f, unused)));
+      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
 #undef PNTF_WAIT0
+#undef PNTF_WAIT0_Y1
 #undef PNTF_WAIT1
 #undef PNTF_DB
       // g13s is rewritten by the next tile's seeds only after every thread has left step 12 of this tile:
