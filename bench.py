@@ -49,7 +49,8 @@ def parse():
     ap.add_argument("--cpu-chunks", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--plan", action="store_true", help="also report the path-integration metric in `extra`")
+    ap.add_argument("--plan", action="store_true", help="(default on; kept for compatibility)")
+    ap.add_argument("--no-plan", action="store_true", help="skip the path-integration metric in `extra`")
     return ap.parse_args()
 
 
@@ -281,7 +282,7 @@ def run_b200(args):
                 reducer(fp.grad, torch.stack([loss.detach(), loss_n.detach()]))
             opt.step(grad_scale=1.0 / world)
             opt.zero_grad()
-            return float(loss_n)                                            # D2H read of the step's loss
+            return float(loss_n.detach())                                   # D2H read of the step's loss
 
         for _ in range(max(1, min(args.warmup, 2))):
             step_e2e()
@@ -308,7 +309,7 @@ def run_b200(args):
     pk = peaks()
     fl = FWD_FLOP[d]
     # algorithmic FLOPs each kernel class is responsible for, per pair
-    class_flop = {"forward": fl, "reverse": fl, "dw": fl, "tc_forward": fl, "tc_reverse": 2 * fl, "tc_dw": fl}
+    class_flop = {"forward": fl, "reverse": fl, "dw": fl, "tc_forward": fl, "tc_reverse": fl, "tc_dw": fl}
     top = max(prof.items(), key=lambda kv: kv[1][0])
     top_name, (top_ms, top_cnt) = top
     step_ms_kernels = sum(v[0] for v in prof.values())
@@ -333,7 +334,7 @@ def run_b200(args):
                          % (args.cpu_chunks, args.cpu_pairs)}
 
     extra = {}
-    if args.plan:
+    if not args.no_plan:
         extra["plan"] = plan_metric(model, B, d, dev)
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -350,25 +351,41 @@ def run_b200(args):
 
 
 def plan_metric(model, B, d, dev, Q=65536):
-    """Secondary metric: batched bidirectional path integration, paths/s (BASELINE configs[4])."""
+    """Secondary metric: batched bidirectional path integration, paths/s (BASELINE configs[4]): 65 536 start/goal
+    queries ~ U[-0.4,0.4]^d, reference step / threshold / cap (test/gib_plan.py:74-86, test/arm_plan.py:140-152), on
+    freshly initialised weights (the trained weights of the timed steps are left alone)."""
     import torch
-    from pntf import synth
+    from pntf import capi, synth
+    from pntf.model import Model_multi
     q = synth.sample_queries(Q, d, dev)
     eta, thr, cap = (0.03, 0.06, 500) if d == 3 else (0.015, 0.03, 300)
-    model.B = B[0]
-    res = {}
+    torch.manual_seed(0)
+    fresh = Model_multi("", "", d, 1, device=str(dev))
+    fresh.init_network()
+    flat = fresh.network.flat().flat
+    Bq = B[:1].contiguous()
+    res = {"queries": Q, "eta": eta, "thr": thr, "max_iter": cap}
     for mode in (("compat", "exact") if d == 3 else ("exact",)):
-        model.plan(q[:1024], B=B[:1], step=eta, thr=thr, max_iter=cap, grad_mode=mode)
-        torch.cuda.synchronize()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        way, nst = model.plan(q, B=B[:1], step=eta, thr=thr, max_iter=cap, grad_mode=mode)
-        b.record()
-        torch.cuda.synchronize()
-        ms = a.elapsed_time(b)
-        steps = float(nst.float().sum().item())
-        res[mode] = {"paths_per_s": Q / (ms * 1e-3), "path_steps_per_s": steps / (ms * 1e-3), "mean_steps": steps / Q,
-                     "ms": ms, "waypoint_GBps": steps * 2 * d * 4 / (ms * 1e-3) / 1e9}
+        fl = capi.GRAD_COMPAT if mode == "compat" else capi.GRAD_EXACT
+        for prec_name, prec in (("tc", capi.PREC_TC), ("fp32_simt", capi.PREC_FP32)):
+            if prec_name == "fp32_simt" and mode != "exact":
+                continue
+            if prec_name == "tc":      # warm-up at full size (the waypoint buffer comes from torch's caching allocator)
+                capi.plan(flat, Bq, q, d, eta, thr, cap, fl, prec=prec)
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            way, nst = capi.plan(flat, Bq, q, d, eta, thr, cap, fl, prec=prec)
+            b.record()
+            torch.cuda.synchronize()
+            ms = a.elapsed_time(b)
+            steps = float(nst.float().sum().item())
+            res["%s_%s" % (mode, prec_name)] = {
+                "paths_per_s": Q / (ms * 1e-3), "path_steps_per_s": steps / (ms * 1e-3), "mean_steps": steps / Q,
+                "ms": ms, "finite": bool(torch.isfinite(way).all().item()),
+                "alg_waypoint_GBps": steps * 2 * d * 4 / (ms * 1e-3) / 1e9,
+                "written_GBps": way.numel() * 4 / (ms * 1e-3) / 1e9,
+                "alg_tflops": steps * 2621952 / (ms * 1e-3) / 1e12 if d == 3 else None}
     return res
 
 

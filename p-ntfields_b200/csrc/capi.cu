@@ -388,8 +388,10 @@ int pntf_plan(const float* params, const float* B, const float* start_goal, int6
   if (int rc = check_common(params, B, start_goal, 1, Q, d)) return rc;
   if (!waypoints || !nsteps || max_iter < 0) return fail(PNTF_ERR_ARG, "bad plan argument");
   if (Q == 0) return PNTF_OK;
+  if (prec == PNTF_PREC_TC)
+    return tc_plan(params, B, start_goal, Q, d, eta, thr, max_iter, grad_flavour, waypoints, nsteps, workspace,
+                   workspace_bytes, stream);
   if (!workspace || workspace_bytes < kPackedBytes) return fail(PNTF_ERR_WORKSPACE, "workspace too small");
-  (void)prec;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   float* packed = static_cast<float*>(workspace);
   if (int rc = pack(params, packed, nullptr, d, s)) return rc;

@@ -23,6 +23,10 @@ size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes);
 int tc_forward(int mode, int grad_flavour, const float* params, const float* B, const float* coords, int E, int64_t N,
                int d, float* tau, float* dtau, float* ltau, void* workspace, size_t workspace_bytes, void* stream);
 
+int tc_plan(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta, float thr,
+            int max_iter, int grad_flavour, float* waypoints, int32_t* nsteps, void* workspace, size_t workspace_bytes,
+            void* stream);
+
 // with_grad = 0: Model.Loss forward; 1: forward + parameter gradients
 int tc_loss(int with_grad, int variant, const float* params, const float* B, const float* coords, const float* speed,
             int E, int64_t N, int d, float alpha, float beta, float gamma, float* diff, float* loss_out,

@@ -31,7 +31,7 @@
 namespace pntf {
 namespace tc {
 
-enum { TC_TAIL_NONE = 0, TC_TAIL_LOSS = 1, TC_TAIL_FIELD = 2 };
+enum { TC_TAIL_NONE = 0, TC_TAIL_LOSS = 1, TC_TAIL_FIELD = 2, TC_TAIL_PLAN = 3 };
 
 struct TcStash {
   uint8_t* X[kNumLayers];   // fp16 operand-tile images of the layer inputs, [tile][K_l * 256 B], l = 0..13
@@ -54,6 +54,12 @@ struct TcFwdArgs {
   int compat;
   TcStash st;
   long long* trace;         // debug (PNTF_TRACE=1): clock64 time stamps of CTA 0's third tile, else nullptr
+  // TC_TAIL_PLAN (batched path integration, test/gib_plan.py:53-86): coords = start/goal queries
+  float eta, thr;
+  int max_iter;
+  float* waypoints;         // [Q][max_iter+2][2D]
+  int32_t* nsteps;          // [Q]
+  int* tile_counter;        // zeroed by the host: tiles of queries are handed out dynamically
 };
 
 // debug time stamps: slot layout [role][layer][event]
@@ -271,6 +277,10 @@ struct TcCtl {
   uint64_t sd[2][2];            // stash store of a buffer half h has finished reading shared memory; successive
                                 // events alternate between two barriers (a waiter may lag two events behind)
   uint32_t tmem_base;
+  // TC_TAIL_PLAN: the number of passes is data dependent; an epilogue thread announces every pass
+  uint64_t go;                  // completes once per announcement
+  volatile int more;            // 1 = another pass follows, 0 = the CTA is done
+  volatile int next_tile;
 };
 
 // all epilogue threads: half h of the next operand tile (and its TMEM pre-loads) is complete
@@ -313,6 +323,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
   using C = TcCfg<D, ORDER>;
   constexpr int S = kFwdRing;
   constexpr int CGP = C::CGP, P = C::P;
+  constexpr bool PLAN = (TAIL == TC_TAIL_PLAN);
+  static_assert(!PLAN || (ORDER == 1 && !TRAIN), "path integration runs the first-order forward");
   constexpr int ACC_A = 0, ACC_B = 256;       // TMEM accumulator regions (columns)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -330,6 +342,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     mbar_init(&ctl.ar[0], 1);
     mbar_init(&ctl.ar[1], 1);
     for (int i = 0; i < 4; ++i) mbar_init(&ctl.sd[i >> 1][i & 1], 1);
+    mbar_init(&ctl.go, 1);
     fence_barrier_init();
   }
   if (warp == kMmaWarp) tmem_alloc(&ctl.tmem_base, 512);
@@ -342,8 +355,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
   if (warp == kProducerWarp) {
     // ------------------------------------------------------------- weight-stage producer
     if (lane_id == 0) {
-      uint32_t it = 0;
-      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      uint32_t it = 0, npass = 0;
+      for (int64_t tile = blockIdx.x; PLAN || tile < ntiles; tile += gridDim.x) {
+        if constexpr (PLAN) {
+          mbar_wait(&ctl.go, npass & 1);
+          ++npass;
+          if (!ctl.more) break;
+        }
         for (int g = 0; g < kFwdStages; ++g) {
           const uint32_t slot = it % S, ph = (it / S) & 1;
           mbar_wait(&ctl.empty[slot], ph ^ 1);
@@ -355,9 +373,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     }
   } else if (warp == kMmaWarp) {
     // ------------------------------------------------------------- MMA issuer (converged warp, elected lane issues)
-    uint32_t it = 0, nx0 = 0, nx1 = 0;
+    uint32_t it = 0, nx0 = 0, nx1 = 0, npass = 0;
     const uint32_t ring_addr = smem_u32(ring), act_addr = smem_u32(act);
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (int64_t tile = blockIdx.x; PLAN || tile < ntiles; tile += gridDim.x) {
+      if constexpr (PLAN) {
+        mbar_wait(&ctl.go, npass & 1);
+        ++npass;
+        if (!ctl.more) break;
+      }
 #pragma unroll 1
       for (int l = 0; l < kNumLayers; ++l) {
         const int K = c_K[l], KH = K >> 7, MH = halves(c_M[l]);
@@ -430,11 +453,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
 #pragma unroll
       for (int i = 0; i < 2 * D; ++i) t.x[tid][i] = valid ? __ldg(a.coords + pair * 2 * D + i) : 0.f;
     };
-    if (tid < P) {
-      load_tile(blockIdx.x, ts[0]);
-      load_tile(int64_t(blockIdx.x) + gridDim.x, ts[1]);
+    if constexpr (!PLAN) {
+      if (tid < P) {
+        load_tile(blockIdx.x, ts[0]);
+        load_tile(int64_t(blockIdx.x) + gridDim.x, ts[1]);
+      }
+      named_bar_sync(1, kEpiThreads);
     }
-    named_bar_sync(1, kEpiThreads);
     int par = 0;
     uint32_t nsd0 = 0, nsd1 = 0;
     const uint32_t buf0 = act_addr, buf1 = act_addr + kTileBytes;
@@ -446,11 +471,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
 #define PNTF_WAIT_ACC1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); trace_evt(a.trace, tron, trole, tl, 2); }
 #define PNTF_PUB(h) { epi_publish(&ctl.xr[h]); trace_evt(a.trace, tron, trole, tl < 0 ? 15 : tl, 1 + 2 * (h)); }
     const int trole = (tid == 0) ? 1 : 2;
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
-      const int64_t pair0 = a.pair_begin + tile * P;
-      const bool first = tile == int64_t(blockIdx.x);
+    // One pass of a tile through the network: Fourier features .. output layer; leaves the output layer's
+    // pre-activation rows in y13s[par] (visible to all epilogue threads on return).
+    auto pass = [&](bool first, int par, bool tron_tile) {
       int tl = -1;
-      const bool tron = (tid == 0 || tid == kEpiThreads - 1) && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x;
+      const bool tron = (tid == 0 || tid == kEpiThreads - 1) && tron_tile;
       if (!first) {   // buffer 0 was last occupied by X12 of the previous tile (sd[1] also delivers X11's second half)
         PNTF_WAIT_SD0();
         PNTF_WAIT_SD1();
@@ -535,6 +560,80 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
       }
       tc_fence_before();
       named_bar_sync(1, kEpiThreads);
+    };
+    if constexpr (PLAN) {
+      // ---- batched bidirectional path integration: per tile of P queries iterate XP += eta * Gradient(XP) until the
+      // endpoints of every query met (|x1 - x0| <= thr) or max_iter + 1 steps were taken (test/gib_plan.py:74-86)
+      __shared__ int active[P];
+      __shared__ int steps_s[P];
+      const int64_t wstride = int64_t(a.max_iter + 2) * 2 * D;
+      TcTile<C>& t0 = ts[0];
+      for (;;) {
+        if (tid == 0) ctl.next_tile = atomicAdd(a.tile_counter, 1);
+        named_bar_sync(1, kEpiThreads);
+        const int64_t tile = ctl.next_tile;
+        if (tile >= ntiles) break;
+        const int64_t pair0 = a.pair_begin + tile * P;
+        if (tid < P) {
+          load_tile(tile, t0);
+          float d2 = 0.f;
+#pragma unroll
+          for (int i = 0; i < D; ++i) { const float dv = t0.x[tid][D + i] - t0.x[tid][i]; d2 = fmaf(dv, dv, d2); }
+          active[tid] = t0.valid[tid] && sqrtf(d2) > a.thr;
+          steps_s[tid] = 0;
+          if (t0.valid[tid])
+            for (int i = 0; i < 2 * D; ++i) a.waypoints[(pair0 + tid) * wstride + i] = t0.x[tid][i];
+        }
+        named_bar_sync(1, kEpiThreads);
+#pragma unroll 1
+        for (int it = 1; it <= a.max_iter + 1; ++it) {
+          int any = 0;
+#pragma unroll
+          for (int q = 0; q < P; ++q) any |= active[q];
+          if (!any) break;
+          if (tid == 0) {
+            ctl.more = 1;
+            mbar_arrive(&ctl.go);
+          }
+          pass(false, 0, false);
+          if (tid < P && active[tid]) {
+            float y[CGP];
+#pragma unroll
+            for (int c = 0; c < CGP; ++c) y[c] = y13s[0][tid * CGP + c];
+            y[0] += __ldg(prm + c_b[13]);
+            const ActOut o = actout_eval(y[0]);
+            float dtau[C::N1], dir[2 * D];
+#pragma unroll
+            for (int i = 0; i < C::N1; ++i) dtau[i] = y[1 + i] * o.o1;
+            field_direction<D>(t0.x[tid], o.o, dtau, dir);
+            float d2 = 0.f;
+#pragma unroll
+            for (int i = 0; i < 2 * D; ++i) t0.x[tid][i] = fmaf(a.eta, dir[i], t0.x[tid][i]);
+#pragma unroll
+            for (int i = 0; i < D; ++i) { const float dv = t0.x[tid][D + i] - t0.x[tid][i]; d2 = fmaf(dv, dv, d2); }
+            steps_s[tid] = it;
+            for (int i = 0; i < 2 * D; ++i) a.waypoints[(pair0 + tid) * wstride + int64_t(it) * 2 * D + i] = t0.x[tid][i];
+            if (!(sqrtf(d2) > a.thr)) active[tid] = 0;
+          }
+          named_bar_sync(1, kEpiThreads);
+        }
+        // rows after the last step repeat the final position
+        for (int q = 0; q < P; ++q) {
+          if (!t0.valid[q]) continue;
+          const int64_t base = (pair0 + q) * wstride;
+          const int first_e = (steps_s[q] + 1) * 2 * D, last_e = (a.max_iter + 2) * 2 * D;
+          for (int e = first_e + tid; e < last_e; e += kEpiThreads) a.waypoints[base + e] = t0.x[q][e % (2 * D)];
+        }
+        if (tid < P && t0.valid[tid]) a.nsteps[pair0 + tid] = steps_s[tid];
+      }
+      if (tid == 0) {
+        ctl.more = 0;
+        mbar_arrive(&ctl.go);
+      }
+    } else
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
+      const int64_t pair0 = a.pair_begin + tile * P;
+      pass(tile == int64_t(blockIdx.x), par, blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x);
       if constexpr (TRAIN) {
         if (tid >= 128 && tid < 128 + kRows) a.st.y13[size_t(tile) * kRows + (tid - 128)] = y13s[par][tid - 128];
       }

@@ -94,7 +94,7 @@ static int tc_tile_pairs(int d) { return d <= 3 ? TcCfg<3, 2>::P : TcCfg<6, 2>::
 constexpr size_t kImgBytes = ((kFwdImgBytes + kRevImgBytes + 255) / 256) * 256;
 
 size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes) {
-  if (op != PNTF_OP_LOSS_BWD) return align256(kFwdImgBytes) + 256;
+  if (op != PNTF_OP_LOSS_BWD) return align256(kFwdImgBytes) + 512;
   const size_t P = tc_tile_pairs(d);
   const size_t ntiles = (size_t(E) * size_t(N) + P - 1) / P;
   if (budget_bytes == 0) budget_bytes = size_t(16) << 30;
@@ -215,6 +215,40 @@ int tc_forward(int mode, int grad_flavour, const float* params, const float* B, 
   }
   if (mode == PNTF_MODE_LAPLACE) return tc_launch_forward<6, 2, false, TC_TAIL_NONE>(a, s);
   return tc_launch_forward<6, 1, false, TC_TAIL_NONE>(a, s);
+}
+
+// Batched path integration on the tensor cores: first-order forward per step, queries handed out per tile.
+int tc_plan(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta, float thr,
+            int max_iter, int grad_flavour, float* waypoints, int32_t* nsteps, void* workspace, size_t workspace_bytes,
+            void* stream) {
+  if (Q == 0) return PNTF_OK;
+  if (int rc = tc_check_ws(workspace, workspace_bytes, align256(kFwdImgBytes) + 256)) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  uint8_t* img = static_cast<uint8_t*>(workspace);
+  int* counter = reinterpret_cast<int*>(img + align256(kFwdImgBytes));
+  if (int rc = tc_pack(params, img, nullptr, s)) return rc;
+  cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), s);
+  if (e != cudaSuccess) return fail(PNTF_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
+  TcFwdArgs a{};
+  a.params = params; a.wimg = img; a.B = B; a.coords = start_goal;
+  a.n_total = Q; a.n_per_env = Q; a.pair_begin = 0; a.pair_count = Q;
+  a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
+  a.eta = eta; a.thr = thr; a.max_iter = max_iter; a.waypoints = waypoints; a.nsteps = nsteps; a.tile_counter = counter;
+  const int64_t P = (d == 3) ? TcCfg<3, 1>::P : TcCfg<6, 1>::P;
+  const int64_t ntiles = (Q + P - 1) / P;
+  const int grid = int(ntiles < sm_count() ? ntiles : sm_count());
+  prof_start(KC_PLAN, s);
+  if (d == 3) {
+    auto k = tc_forward_kernel<3, 1, false, TC_TAIL_PLAN>;
+    if (int rc = tc_set_smem(k, kFwdSmem)) return rc;
+    k<<<grid, kTcThreads, kFwdSmem, s>>>(a);
+  } else {
+    auto k = tc_forward_kernel<6, 1, false, TC_TAIL_PLAN>;
+    if (int rc = tc_set_smem(k, kFwdSmem)) return rc;
+    k<<<grid, kTcThreads, kFwdSmem, s>>>(a);
+  }
+  prof_stop(s);
+  return launch_check("tc_plan");
 }
 
 int tc_loss(int with_grad, int variant, const float* params, const float* B, const float* coords, const float* speed,

@@ -127,7 +127,8 @@ class _ModelBase:
         sg = start_goal.to(device=dev, dtype=torch.float32).contiguous()
         Bd = B.to(device=dev, dtype=torch.float32).contiguous()
         flav = capi.GRAD_COMPAT if grad_mode == 'compat' else capi.GRAD_EXACT
-        return capi.plan(self.network.flat().flat, Bd, sg, self.dim, step, thr, max_iter, flav)
+        return capi.plan(self.network.flat().flat, Bd, sg, self.dim, step, thr, max_iter, flav,
+                         prec=_PREC[self.network.precision])
 
     @staticmethod
     def path(waypoints, nsteps, q, dim):

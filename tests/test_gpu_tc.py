@@ -119,3 +119,28 @@ def test_tc_param_grads_vs_oracle_autograd(capi, d, variant, E, N, budget_tiles)
             assert bool((gk == 0).all())
         else:
             assert rel_err(gk, ref) < 2e-2, (k, rel_err(gk, ref))
+
+
+@pytest.mark.parametrize("d,Q,cap,mode", [(3, 19, 12, "exact"), (3, 333, 40, "compat"), (6, 50, 25, "exact")])
+def test_tc_plan_vs_oracle(capi, d, Q, cap, mode):
+    """Batched bidirectional path integration on the tensor cores (first-order forward per step, dynamic tiles of
+    queries) against the oracle loop: waypoints within 1e-3 of the workspace scale (unit box)."""
+    rs = np.random.RandomState(9)
+    P = O.init_params(8)
+    Bw = (0.5 * rs.normal(size=(d, 128))).astype(np.float32)
+    sg = rs.uniform(-0.4, 0.4, size=(Q, 2 * d)).astype(np.float32)
+    sg[3, d:] = sg[3, :d] + 0.005          # already within thr: zero steps
+    eta, thr = (0.03, 0.06) if d == 3 else (0.015, 0.03)
+    with torch.no_grad():
+        way, nst = O.plan(P, T(sg), T(Bw), eta, thr, cap, mode)
+    fl = capi.GRAD_COMPAT if mode == "compat" else capi.GRAD_EXACT
+    w2, n2 = capi.plan(flat_from(P), cu(Bw).view(1, d, 128), cu(sg), d, eta, thr, cap, fl, prec=capi.PREC_TC)
+    n2 = n2.cpu().numpy()
+    w2 = w2.cpu().numpy()
+    assert n2[3] == 0
+    same = n2 == nst.numpy()
+    # a query whose final distance is within rounding of thr may take one step more or less
+    assert same.mean() > 0.97 and np.abs(n2 - nst.numpy()).max() <= 1
+    assert np.abs(w2[same] - way.numpy()[same]).max() < 1e-3
+    for q in range(Q):
+        assert np.all(w2[q, n2[q]:] == w2[q, n2[q]])
