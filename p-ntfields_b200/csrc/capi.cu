@@ -306,7 +306,10 @@ int pntf_field(int kind, int grad_flavour, const float* params, const float* B, 
   if (grad_flavour == PNTF_GRAD_COMPAT && kind != PNTF_FIELD_DIRECTION)
     return fail(PNTF_ERR_ARG, "the compat gradient flavour exists for FIELD_DIRECTION only");
   const int order = (kind == PNTF_FIELD_TRAVEL_TIME) ? 0 : (kind == PNTF_FIELD_SPEED2 ? 2 : 1);
-  (void)prec;   // fields run on the fp32 path in both precisions (inference-sized batches)
+  if (prec == PNTF_PREC_TC) {
+    if (int rc = check_common(params, B, coords, E, N, d)) return rc;
+    return tc_field(kind, grad_flavour, params, B, coords, E, N, d, gamma, out, workspace, workspace_bytes, stream);
+  }
   return forward_common(order, TAIL_FIELD, kind, grad_flavour, params, B, coords, nullptr, E, N, d, 1.f, gamma, 0,
                         nullptr, nullptr, nullptr, out, nullptr, workspace, workspace_bytes, stream);
 }

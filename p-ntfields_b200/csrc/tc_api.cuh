@@ -23,6 +23,9 @@ size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes);
 int tc_forward(int mode, int grad_flavour, const float* params, const float* B, const float* coords, int E, int64_t N,
                int d, float* tau, float* dtau, float* ltau, void* workspace, size_t workspace_bytes, void* stream);
 
+int tc_field(int kind, int grad_flavour, const float* params, const float* B, const float* coords, int E, int64_t N,
+             int d, float gamma, float* out, void* workspace, size_t workspace_bytes, void* stream);
+
 int tc_plan(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta, float thr,
             int max_iter, int grad_flavour, float* waypoints, int32_t* nsteps, void* workspace, size_t workspace_bytes,
             void* stream);

@@ -217,6 +217,28 @@ int tc_forward(int mode, int grad_flavour, const float* params, const float* B, 
   return tc_launch_forward<6, 1, false, TC_TAIL_NONE>(a, s);
 }
 
+// Model.TravelTimes / Speed / Speed2 / Gradient on the tensor cores (forward kernel with the field tail)
+int tc_field(int kind, int grad_flavour, const float* params, const float* B, const float* coords, int E, int64_t N,
+             int d, float gamma, float* out, void* workspace, size_t workspace_bytes, void* stream) {
+  if (N == 0) return PNTF_OK;
+  if (int rc = tc_check_ws(workspace, workspace_bytes, kFwdImgBytes)) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  uint8_t* img = static_cast<uint8_t*>(workspace);
+  if (int rc = tc_pack(params, img, nullptr, s)) return rc;
+  TcFwdArgs a{};
+  a.params = params; a.wimg = img; a.B = B; a.coords = coords;
+  a.n_total = int64_t(E) * N; a.n_per_env = N; a.pair_begin = 0; a.pair_count = a.n_total;
+  a.field = out; a.field_kind = kind; a.gamma = gamma;
+  a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
+  const bool second = (kind == PNTF_FIELD_SPEED2);
+  if (d == 3) {
+    if (second) return tc_launch_forward<3, 2, false, TC_TAIL_FIELD>(a, s);
+    return tc_launch_forward<3, 1, false, TC_TAIL_FIELD>(a, s);
+  }
+  if (second) return tc_launch_forward<6, 2, false, TC_TAIL_FIELD>(a, s);
+  return tc_launch_forward<6, 1, false, TC_TAIL_FIELD>(a, s);
+}
+
 // Batched path integration on the tensor cores: first-order forward per step, queries handed out per tile.
 int tc_plan(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta, float thr,
             int max_iter, int grad_flavour, float* waypoints, int32_t* nsteps, void* workspace, size_t workspace_bytes,

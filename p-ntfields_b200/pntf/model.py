@@ -220,7 +220,8 @@ class Model_single(_ModelBase):
     def _field(self, kind, Xp, gamma=0.0, flavour=capi.GRAD_EXACT):
         Xp = Xp.detach().to(device=self._dev(), dtype=torch.float32).contiguous()
         B = self.network.B.to(dtype=torch.float32).contiguous()
-        return capi.field(kind, self.network.flat().flat, B, Xp, 1, Xp.shape[0], self.dim, gamma, grad_flavour=flavour)
+        return capi.field(kind, self.network.flat().flat, B, Xp, 1, Xp.shape[0], self.dim, gamma, grad_flavour=flavour,
+                          prec=_PREC[self.network.precision])
 
     def TravelTimes(self, Xp):
         return self._field(capi.FIELD_TRAVEL_TIME, Xp)
@@ -298,7 +299,8 @@ class Model_multi(_ModelBase):
     def _field(self, kind, Xp, B, gamma=0.0, flavour=capi.GRAD_EXACT):
         Xp = Xp.detach().to(device=self._dev(), dtype=torch.float32).contiguous()
         Bd = B.detach().to(device=self._dev(), dtype=torch.float32).contiguous()
-        return capi.field(kind, self.network.flat().flat, Bd, Xp, 1, Xp.shape[0], self.dim, gamma, grad_flavour=flavour)
+        return capi.field(kind, self.network.flat().flat, Bd, Xp, 1, Xp.shape[0], self.dim, gamma, grad_flavour=flavour,
+                          prec=_PREC[self.network.precision])
 
     def TravelTimes(self, Xp):
         return self._field(capi.FIELD_TRAVEL_TIME, Xp, self.B)

@@ -69,8 +69,8 @@ class _NNBase(torch.nn.Module):
         self.generator.append(Linear(h, 1))
         self._fp = None
         self._device = torch.device(device)
-        #: 'fp32' = fp32 SIMT verify mode, 'tc' = tcgen05 tensor-core mode
-        self.precision = "fp32"
+        #: 'tc' = tcgen05 tensor-core mode (fp16 operands, fp32 accumulation), 'fp32' = fp32 SIMT verify mode
+        self.precision = "tc"
         #: bytes of activation stash pntf_loss_bwd may use (0 = library default)
         self.stash_budget = 0
 
@@ -111,7 +111,7 @@ class _NNBase(torch.nn.Module):
         B = B.detach().to(device=coords.device, dtype=torch.float32).contiguous()
         fp = self.flat()
         return capi.forward(mode, fp.flat, B, coords.view(E * N, 2 * self.dim), E, N, self.dim,
-                            prec=_PREC[self.precision] if mode == capi.MODE_LAPLACE else capi.PREC_FP32,
+                            prec=_PREC[self.precision],
                             grad_flavour=flavour)
 
 

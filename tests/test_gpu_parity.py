@@ -243,6 +243,7 @@ def test_reference_shaped_api_and_autograd(capi):
     net = M.NN(DEV, d)
     net.load_state_dict(O.init_params(int(fx["seed"])), strict=True)
     net.to(DEV)
+    net.precision = "fp32"          # verify mode: the golden tolerances below are the fp32 ones
     model.network = net
     c, s, B = cu(fx["coords"]), cu(fx["speed"]), cu(fx["B"])
     tau, dtau, ltau, Xp = net.out_laplace(c, B)
@@ -277,6 +278,7 @@ def test_reference_shaped_api_and_autograd(capi):
     ns = S.NN(DEV, 6, T(fs["B"]))
     ns.load_state_dict(O.init_params(int(fs["seed"])), strict=True)
     ns.to(DEV)
+    ns.precision = "fp32"
     ms.network = ns
     loss, loss_n, diff = ms.Loss(cu(fs["coords"]), cu(fs["speed"]), float(fs["beta"]), float(fs["gamma"]))
     assert abs(loss.item() - fs["loss"]) / abs(fs["loss"]) < 1e-5

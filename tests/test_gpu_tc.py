@@ -144,3 +144,44 @@ def test_tc_plan_vs_oracle(capi, d, Q, cap, mode):
     assert np.abs(w2[same] - way.numpy()[same]).max() < 1e-3
     for q in range(Q):
         assert np.all(w2[q, n2[q]:] == w2[q, n2[q]])
+
+
+def test_tc_reference_shaped_api(capi):
+    """The drop-in classes default to the tensor-core mode: NN.out / out_grad / out_laplace, Model.Loss + backward,
+    TravelTimes / Speed / Speed2 / Gradient and plan against the reference-generated golden fixtures at the
+    north-star tolerances (tau 1e-3, speed / loss 1e-2)."""
+    import os
+    from models import model_res_sigmoid_multi as M, model_res_sigmoid as S
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    fx = np.load(os.path.join(gold, "multi_d3.npz"))
+    d = 3
+    model = M.Model("/tmp", "/tmp", d, 2, device=DEV)
+    net = M.NN(DEV, d)
+    net.load_state_dict(O.init_params(int(fx["seed"])), strict=True)
+    net.to(DEV)
+    assert net.precision == "tc"
+    model.network = net
+    c, s, B = cu(fx["coords"]), cu(fx["speed"]), cu(fx["B"])
+    tau, dtau, ltau, _ = net.out_laplace(c, B)
+    assert pointwise_rel(tau.cpu().numpy().reshape(-1), fx["lap_tau"].reshape(-1)) < 1e-3
+    assert rel_err(ltau.cpu(), fx["lap_ltau"]) < 3e-2
+    loss, loss_n, diff = model.Loss(c, s, B, float(fx["beta"]), float(fx["gamma"]))
+    assert abs(loss.item() - float(fx["loss"])) / abs(float(fx["loss"])) < 1e-2
+    loss.backward()
+    assert dict(net.named_parameters())["encoder1.0.weight"].grad is None
+    model.B = B[0]
+    assert rel_err(model.TravelTimes(c[0]).cpu(), fx["travel_times"]) < 1e-3
+    assert rel_err(model.Speed(c[0]).cpu(), fx["speed_pred"]) < 1e-2
+    assert rel_err(model.Gradient(c[0], B[0]).cpu(), fx["gradient"]) < 1e-2
+    way, nst = model.plan(cu(fx["plan_start_goal"]), B[0], 0.03, 0.06, 500)
+    assert np.abs(nst.cpu().numpy() - fx["plan_nsteps"]).max() <= 1
+
+    fs = np.load(os.path.join(gold, "single_d6.npz"))
+    ms = S.Model("/tmp", "/tmp", 6, device=DEV)
+    ns = S.NN(DEV, 6, T(fs["B"]))
+    ns.load_state_dict(O.init_params(int(fs["seed"])), strict=True)
+    ns.to(DEV)
+    ms.network = ns
+    loss, loss_n, diff = ms.Loss(cu(fs["coords"]), cu(fs["speed"]), float(fs["beta"]), float(fs["gamma"]))
+    assert abs(loss.item() - fs["loss"]) / abs(fs["loss"]) < 1e-2
+    assert rel_err(ms.Speed2(cu(fs["coords"]), float(fs["gamma"])).cpu(), fs["speed2_pred"]) < 1e-2
