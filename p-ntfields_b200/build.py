@@ -21,16 +21,18 @@ def newest_source_mtime():
     return m
 
 
-def build(force=False, verbose=False):
-    if not force and os.path.exists(OUT) and os.path.getmtime(OUT) >= newest_source_mtime():
-        return OUT
+def build(force=False, verbose=False, defs=(), out=None, objdir="build"):
+    """defs / out: experiment builds (scripts/build_variants.py) with extra -D flags into another file."""
+    global_out = out or OUT
+    if not force and os.path.exists(global_out) and os.path.getmtime(global_out) >= newest_source_mtime():
+        return global_out
     objs = []
-    os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    os.makedirs(os.path.join(HERE, objdir), exist_ok=True)
     procs = []
     for src in SOURCES:
-        obj = os.path.join(HERE, "build", src.replace(".cu", ".o"))
+        obj = os.path.join(HERE, objdir, src.replace(".cu", ".o"))
         objs.append(obj)
-        cmd = [NVCC] + FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [NVCC] + FLAGS + list(defs) + ["-c", os.path.join(CSRC, src), "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     for src, p in procs:
         out, _ = p.communicate()
@@ -38,9 +40,9 @@ def build(force=False, verbose=False):
             print(out)
         if p.returncode != 0:
             raise RuntimeError("nvcc failed on %s" % src)
-    cmd = [NVCC, "-shared", "-o", OUT] + objs + ["-lcudart"]
+    cmd = [NVCC, "-shared", "-arch=sm_100a", "-o", global_out] + objs + ["-lcudart"]
     subprocess.check_call(cmd)
-    return OUT
+    return global_out
 
 
 if __name__ == "__main__":

@@ -285,8 +285,20 @@ struct TcCtl {
   volatile int next_tile;
 };
 
-// all epilogue threads: half h of the next operand tile (and its TMEM pre-loads) is complete
+// all epilogue threads (converged warps): half h of the next operand tile (and its TMEM pre-loads) is complete.
+// Every thread fences its own writes; one lane per warp arrives (the barrier counts warps), which keeps the
+// mbarrier unit free for the MMA issuer's polls.
+// Forward kernel: one lane per warp arrives after __syncwarp() (the barrier counts warps): measured -3.5 ms per 1 Mi
+// pairs, the 512 per-thread arrivals compete with the MMA issuer's polls on the mbarrier unit.
 __device__ __forceinline__ void epi_publish(uint64_t* bar) {
+  fence_proxy_async();
+  tc_fence_before();
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
+}
+// Reverse kernel: every thread arrives as soon as it is done (measured 2 ms faster there than the per-warp form:
+// its epilogues are longer and more skewed across lanes).
+__device__ __forceinline__ void epi_publish_each(uint64_t* bar) {
   fence_proxy_async();
   tc_fence_before();
   mbar_arrive(bar);
@@ -294,6 +306,10 @@ __device__ __forceinline__ void epi_publish(uint64_t* bar) {
 
 // MMA issue of one (contraction half kh, output half h) block: 2 stages x 4 UMMAs.  Called by the whole
 // (converged) MMA warp; one elected lane issues.
+// Measured (scripts/umma_bench.cu, profiles/r01c_umma_microbench.md): a poll of a ready mbarrier costs the issuing
+// warp 100-250 clk and the UMMA queue is shallow, so the per-stage poll + commit keeps the pipe at ~110-130 clk per
+// UMMA (floor 64).  A ring of three 32 KB blocks (one poll per 8 UMMAs, same smem look-ahead) was tried and was
+// 4 ms per 1 Mi pairs SLOWER in the training forward (coarser slot release), so the 16 KB stages stay.
 template <int S, class CTL>
 __device__ __forceinline__ void mma_block(CTL* ctl, uint32_t ring_addr, uint32_t opnd_addr, uint32_t d_tmem, int kh,
                                           bool accumulate_first, uint32_t& it) {
@@ -339,8 +355,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
   const int tid = threadIdx.x, warp = tid >> 5, lane_id = tid & 31;
   if (tid == 0) {
     for (int i = 0; i < S; ++i) { mbar_init(&ctl.full[i], 1); mbar_init(&ctl.empty[i], 1); }
-    mbar_init(&ctl.xr[0], kEpiThreads);
-    mbar_init(&ctl.xr[1], kEpiThreads);
+    mbar_init(&ctl.xr[0], kEpiWarps);
+    mbar_init(&ctl.xr[1], kEpiWarps);
     mbar_init(&ctl.ar[0], 1);
     mbar_init(&ctl.ar[1], 1);
     for (int i = 0; i < 4; ++i) mbar_init(&ctl.sd[i >> 1][i & 1], 1);

@@ -372,48 +372,48 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
       if (tile != int64_t(blockIdx.x)) PNTF_WAIT_SD0();
       { mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; trace_evt(a.trace, tron, 1, 12, 1); }
       PNTF_DB(12, 0, (epi_adjoint_half<C, false, false, true>(p, 0, 0, p.lane, x_addr, gt_addr, g13s, w13f, dw13)));
-      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+      { epi_publish_each(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
 #pragma unroll 1
       for (int l = 11; l >= 6; --l) {
         const bool second = (l & 1) != 0;      // second layer of a block: reads B, pre-loads the skip adjoint in place
         if (second) {
           PNTF_WAIT0();
           PNTF_DB(l, 0, (epi_adjoint_half<C, false, true, false>(p, ACC_B, ACC_B, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
-          { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+          { epi_publish_each(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
           PNTF_WAIT1();
           PNTF_DB(l, 1, (epi_adjoint_half<C, false, true, false>(p, ACC_B + 128, ACC_B + 128, 128 + p.lane, x_addr, gt_addr,
                                                                   nullptr, 0.f, unused)));
-          { epi_publish(&ctl.xr[1]); trace_evt(a.trace, tron, 1, tl, 3); }
+          { epi_publish_each(&ctl.xr[1]); trace_evt(a.trace, tron, 1, tl, 3); }
         } else {
           PNTF_WAIT0();
           PNTF_DB(l, 0, (epi_adjoint_half<C, false, false, false>(p, ACC_A, 0, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
-          { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+          { epi_publish_each(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
           PNTF_WAIT1();
           PNTF_DB(l, 1, (epi_adjoint_half<C, false, false, false>(p, ACC_A + 128, 0, 128 + p.lane, x_addr, gt_addr, nullptr,
                                                                    0.f, unused)));
-          { epi_publish(&ctl.xr[1]); trace_evt(a.trace, tron, 1, tl, 3); }
+          { epi_publish_each(&ctl.xr[1]); trace_evt(a.trace, tron, 1, tl, 3); }
         }
       }
       // ---- combine (needs both halves of the adjoint of its output) and encoder
       PNTF_WAIT0();
       { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); }
       PNTF_DB(5, 0, epi_combine_adjoint<C>(p, ACC_B, x_addr, gt_addr));
-      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+      { epi_publish_each(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
       PNTF_WAIT0_Y1();
       PNTF_DB(4, 0, (epi_adjoint_half<C, true, true, false>(p, ACC_A, ACC_B, p.lane, x_addr + kHalfTileBytes, gt_addr, nullptr, 0.f, unused)));
-      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+      { epi_publish_each(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
       PNTF_WAIT0();
       PNTF_DB(3, 0, (epi_adjoint_half<C, true, false, false>(p, ACC_A, 0, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
-      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+      { epi_publish_each(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
       PNTF_WAIT0_Y1();
       PNTF_DB(2, 0, (epi_adjoint_half<C, true, true, false>(p, ACC_B, ACC_B, p.lane, x_addr + kHalfTileBytes, gt_addr, nullptr, 0.f, unused)));
-      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+      { epi_publish_each(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
       PNTF_WAIT0();
       PNTF_DB(1, 0, (epi_adjoint_half<C, true, false, false>(p, ACC_A, 0, p.lane, x_addr, gt_addr, nullptr, 0.f, unused)));
-      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+      { epi_publish_each(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
       PNTF_WAIT0_Y1();
       PNTF_DB(0, 0, (epi_adjoint_half<C, true, false, false>(p, ACC_B, 0, p.lane, x_addr + kHalfTileBytes, gt_addr, nullptr, 0.f, unused)));
-      { epi_publish(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
+      { epi_publish_each(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
 #undef PNTF_WAIT0
 #undef PNTF_WAIT0_Y1
 #undef PNTF_WAIT1
