@@ -33,6 +33,12 @@ UNIT = "pairs/s"
 # algorithmic FLOPs per pair: 14 dense layers, 2 FLOP/MAC, all value/derivative
 # columns; backward = 2x forward (dX and dW)
 FWD_FLOP = {3: 14290176, 6: 27269376}
+# DRAM bytes per pair (dram__bytes_read.sum + dram__bytes_write.sum of one launch / pairs of that launch) from the
+# `ncu --set full` capture profiles/r01c_ncu_full_tc_d3.md (one 99 824-pair chunk, d = 3, tensor-core path);
+# roofline.traffic = this x the pairs one launch of bench.py processes.  No capture for d = 6 / fp32: null.
+NCU_DRAM_BYTES_PER_PAIR = {("tc_forward", 3): (0.150024e9 + 9.406513e9) / 99824,
+                           ("tc_reverse", 3): (7.864236e9 + 7.723717e9) / 99824,
+                           ("tc_dw", 3): (16.357360e9 + 0.006718e9) / 99824}
 
 
 def parse():
@@ -318,8 +324,14 @@ def run_b200(args):
         flops = class_flop[top_name] * n_total * args.steps
         ach = flops / (top_ms * 1e-3) / 1e12
         peak = pk["bf16_sustained"]
+        per_pair = NCU_DRAM_BYTES_PER_PAIR.get((top_name, d))
+        pairs_per_launch = n_total * args.steps / max(top_cnt, 1)
+        traffic = per_pair * pairs_per_launch if per_pair else None
         roof = {"bound": "tensor", "kernel": top_name, "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                "traffic": None, "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
+                "traffic": traffic,
+                "traffic_source": "profiles/r01c_ncu_full_tc_d3.md (ncu --set full, bytes per pair x pairs per launch)" if per_pair else None,
+                "hbm_GBps": (per_pair * n_total * args.steps / (top_ms * 1e-3) / 1e9) if per_pair else None,
+                "hbm_peak_GBps": pk["hbm"], "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
                 "launch_ms_avg": top_ms / max(top_cnt, 1), "launches": top_cnt,
                 "share_of_step": top_ms / max(step_ms_kernels, 1e-9),
                 "alg_flop_per_pair": class_flop[top_name],

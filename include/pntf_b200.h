@@ -93,6 +93,21 @@ int pntf_loss_bwd(int variant, const float* params, const float* B, const float*
                   float* diff, float* loss_out, float* grad_params, int prec,
                   void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same two calls with the batch gather of the training loop fused into the kernels' loads
+ * (models/model_res_sigmoid_multi.py:1053-1066: `data[perm[lo:hi]]`, then points = batch[:, :2d],
+ * speed = batch[:, 2d:]; single: FastTensorDataLoader, models/model_res_sigmoid.py:30-73).
+ * dataset[dataset_rows, 2d+2] is the GPU-resident table in the reference's layout (sampled_points ++ speed,
+ * models/data_multi.py:15-31; several environments are stacked row-wise); pair p of the [E, N] batch is row
+ * index[p] of it.  Nothing is materialised: coordinates and speeds are read through the index. */
+int pntf_loss_fwd_gather(int variant, const float* params, const float* B, const float* dataset, int64_t dataset_rows,
+                         const int32_t* index, int E, int64_t N, int d, float alpha, float beta, float gamma,
+                         float* diff, float* loss_out, int prec,
+                         void* workspace, size_t workspace_bytes, void* stream);
+int pntf_loss_bwd_gather(int variant, const float* params, const float* B, const float* dataset, int64_t dataset_rows,
+                         const int32_t* index, int E, int64_t N, int d, float alpha, float beta, float gamma,
+                         float* diff, float* loss_out, float* grad_params, int prec,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
 /* torch.optim.AdamW step on flat buffers (S:954-956,1074; M:960-962,1079): decoupled weight decay,
  * bias-corrected; elements whose mask byte is 0 are left untouched (parameters with grad None).
  * grad_scale multiplies the gradient first (1/world_size after an all-reduce(sum)).  Hyper-parameters

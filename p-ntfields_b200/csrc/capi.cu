@@ -14,6 +14,7 @@
 namespace pntf {
 
 static thread_local char g_err[512] = "";
+thread_local PairGather g_gather;
 static std::atomic<int64_t> g_launches{0};
 
 int fail(int code, const char* fmt, ...) {
@@ -174,6 +175,7 @@ static int loss_bwd_simt(int variant, const float* params, const float* B, const
     BwdArgs b{};
     FwdArgs& a = b.f;
     a.params = params; a.packed = packed_f; a.B = B; a.coords = coords; a.speed = speed;
+    apply_gather(a, D);
     a.n_total = n_total; a.n_per_env = N; a.pair_begin = begin; a.pair_count = count;
     a.diff = diff; a.single_variant = (variant == PNTF_LOSS_SINGLE); a.alpha = alpha; a.gamma = gamma;
     carve_stash(a.st, stash_base, D, count_pad);
@@ -280,6 +282,7 @@ static int forward_common(int order, int tail, int field_kind, int grad_flavour,
   if (int rc = pack(params, packed, nullptr, d, s)) return rc;
   FwdArgs a{};
   a.params = params; a.packed = packed; a.B = B; a.coords = coords; a.speed = speed;
+  apply_gather(a, d);
   a.n_total = int64_t(E) * N; a.n_per_env = N; a.pair_begin = 0; a.pair_count = a.n_total;
   a.tau = tau; a.dtau = dtau; a.ltau = ltau; a.field = field; a.field_kind = field_kind;
   a.diff = diff; a.single_variant = single_variant; a.alpha = alpha; a.gamma = gamma;
@@ -366,6 +369,37 @@ int pntf_loss_bwd(int variant, const float* params, const float* B, const float*
   return finalize_loss(variant, diff, int64_t(E) * N, B, E, d, beta, loss_out, s);
 }
 
+// ---- fused batch gather: the batch is index[E*N] rows of a GPU-resident dataset
+struct GatherScope {
+  GatherScope(const int32_t* index, int stride) { g_gather.index = index; g_gather.row_stride = stride; }
+  ~GatherScope() { g_gather = PairGather{}; }
+};
+static int check_gather(const float* dataset, int64_t dataset_rows, const int32_t* index, int d) {
+  if (!dataset || !index) return fail(PNTF_ERR_ARG, "null dataset/index");
+  if (d != 3 && d != 6) return fail(PNTF_ERR_ARG, "d must be 3 or 6");
+  if (dataset_rows <= 0 || dataset_rows > int64_t(0x7fffffff)) return fail(PNTF_ERR_ARG, "dataset_rows out of range");
+  return PNTF_OK;
+}
+
+int pntf_loss_fwd_gather(int variant, const float* params, const float* B, const float* dataset, int64_t dataset_rows,
+                         const int32_t* index, int E, int64_t N, int d, float alpha, float beta, float gamma, float* diff,
+                         float* loss_out, int prec, void* workspace, size_t workspace_bytes, void* stream) {
+  if (int rc = check_gather(dataset, dataset_rows, index, d)) return rc;
+  GatherScope scope(index, 2 * d + 2);
+  return pntf_loss_fwd(variant, params, B, dataset, dataset + 2 * d, E, N, d, alpha, beta, gamma, diff, loss_out, prec,
+                       workspace, workspace_bytes, stream);
+}
+
+int pntf_loss_bwd_gather(int variant, const float* params, const float* B, const float* dataset, int64_t dataset_rows,
+                         const int32_t* index, int E, int64_t N, int d, float alpha, float beta, float gamma, float* diff,
+                         float* loss_out, float* grad_params, int prec, void* workspace, size_t workspace_bytes,
+                         void* stream) {
+  if (int rc = check_gather(dataset, dataset_rows, index, d)) return rc;
+  GatherScope scope(index, 2 * d + 2);
+  return pntf_loss_bwd(variant, params, B, dataset, dataset + 2 * d, E, N, d, alpha, beta, gamma, diff, loss_out,
+                       grad_params, prec, workspace, workspace_bytes, stream);
+}
+
 int pntf_adamw(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, const uint8_t* mask, int64_t n,
                double lr, double beta1, double beta2, double eps, double weight_decay, int64_t step,
                double grad_scale, void* stream) {
@@ -401,6 +435,7 @@ int pntf_plan(const float* params, const float* B, const float* start_goal, int6
   PlanArgs pa{};
   FwdArgs& a = pa.f;
   a.params = params; a.packed = packed; a.B = B; a.coords = start_goal;
+  apply_gather(a, d);
   a.n_total = Q; a.n_per_env = Q; a.pair_begin = 0; a.pair_count = Q;
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
   pa.eta = eta; pa.thr = thr; pa.max_iter = max_iter; pa.waypoints = waypoints; pa.nsteps = nsteps;

@@ -7,6 +7,16 @@
 
 namespace pntf {
 
+// Fused batch gather (models/data_multi.py:15-31 and the in-loop `data[perm[lo:hi]]` of
+// models/model_res_sigmoid_multi.py:1053-1064): when `index` is set, pair p of the batch is row index[p] of a
+// GPU-resident dataset whose rows are [2d coordinates, 2 speeds] (cstride = sstride = 2d + 2); otherwise
+// coords / speed are dense [n, 2d] / [n, 2] arrays.
+template <class A>
+__device__ __forceinline__ int64_t src_row(const A& a, int64_t pair) {
+  return a.index != nullptr ? int64_t(__ldg(a.index + pair)) : pair;
+}
+
+
 template <int D>
 struct PairGeom {
   float Dv[D];   // x1 - x0

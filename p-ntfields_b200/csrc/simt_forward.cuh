@@ -17,6 +17,8 @@ struct FwdArgs {
   const float* B;          // [E][D][128]
   const float* coords;     // [n_total][2D]
   const float* speed;      // [n_total][2] or null
+  const int32_t* index;    // optional batch gather (pair_math.cuh: src_row), else null
+  int cstride, sstride;    // row strides of coords / speed in floats (2D / 2 when dense)
   int64_t n_total;         // E*N pairs
   int64_t n_per_env;       // N
   int64_t pair_begin;      // first pair of this launch (chunking)
@@ -47,7 +49,7 @@ __device__ __forceinline__ void load_tile_state(const FwdArgs& a, TileState<C::D
     ts.valid[threadIdx.x] = valid;
     ts.env[threadIdx.x] = valid ? int(pair / a.n_per_env) : 0;
 #pragma unroll
-    for (int i = 0; i < 2 * C::D; ++i) ts.x[threadIdx.x][i] = valid ? __ldg(a.coords + pair * 2 * C::D + i) : 0.f;
+    for (int i = 0; i < 2 * C::D; ++i) ts.x[threadIdx.x][i] = valid ? __ldg(a.coords + src_row(a, pair) * a.cstride + i) : 0.f;
   }
 }
 
@@ -256,8 +258,9 @@ __global__ void __launch_bounds__(kThreads, 1) simt_forward_kernel(const FwdArgs
         }
         const float* x = ts.x[threadIdx.x];
         if constexpr (TAIL == TAIL_LOSS && ORDER == 2) {
-          const float y0 = a.alpha * __ldg(a.speed + pair * 2) + 1.0f - a.alpha;
-          const float y1 = a.alpha * __ldg(a.speed + pair * 2 + 1) + 1.0f - a.alpha;
+          const float* sp = a.speed + src_row(a, pair) * a.sstride;
+          const float y0 = a.alpha * __ldg(sp) + 1.0f - a.alpha;
+          const float y1 = a.alpha * __ldg(sp + 1) + 1.0f - a.alpha;
           a.diff[pair] = eikonal_residual<D, false>(x, tau, dtau, ltau, y0, y1, a.gamma, a.single_variant, 0.f,
                                                     nullptr, nullptr, nullptr);
         }

@@ -93,8 +93,9 @@ __global__ void __launch_bounds__(kThreads, 1) simt_reverse_kernel(const BwdArgs
           dtau[i] = y[1 + i] * o.o1;
           ltau[i] = fmaf(y[1 + i] * y[1 + i], o.o2, y[1 + NG + i] * o.o1);
         }
-        const float y0 = a.alpha * __ldg(a.speed + pair * 2) + 1.0f - a.alpha;
-        const float y1 = a.alpha * __ldg(a.speed + pair * 2 + 1) + 1.0f - a.alpha;
+        const float* sp = a.speed + src_row(a, pair) * a.sstride;
+        const float y0 = a.alpha * __ldg(sp) + 1.0f - a.alpha;
+        const float y1 = a.alpha * __ldg(sp + 1) + 1.0f - a.alpha;
         float tb, db[NG], lb[NG];
         const float diff = eikonal_residual<D, true>(ts.x[p], tau, dtau, ltau, y0, y1, a.gamma, a.single_variant,
                                                      b.wscale, &tb, db, lb);

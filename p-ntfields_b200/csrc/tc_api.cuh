@@ -18,6 +18,20 @@ int sm_count();
 int finalize_loss(int variant, const float* diff, int64_t n_total, const float* B, int E, int d, float beta,
                   float* loss_out, cudaStream_t s);
 
+// Batch source of the current call: dense arrays, or rows of a GPU-resident dataset picked by an index array
+// (pntf_loss_*_gather).  Set by the entry point around the call; one host thread per GPU drives the library.
+struct PairGather {
+  const int32_t* index = nullptr;
+  int row_stride = 0;
+};
+extern thread_local PairGather g_gather;
+template <class A>
+inline void apply_gather(A& a, int d) {
+  a.index = g_gather.index;
+  a.cstride = g_gather.index ? g_gather.row_stride : 2 * d;
+  a.sstride = g_gather.index ? g_gather.row_stride : 2;
+}
+
 size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes);
 
 int tc_forward(int mode, int grad_flavour, const float* params, const float* B, const float* coords, int E, int64_t N,

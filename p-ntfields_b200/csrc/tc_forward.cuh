@@ -46,6 +46,8 @@ struct TcFwdArgs {
   const float* B;           // [E][D][128]
   const float* coords;      // [n_total][2D]
   const float* speed;       // [n_total][2]
+  const int32_t* index;     // optional batch gather (pair_math.cuh: src_row), else null
+  int cstride, sstride;     // row strides of coords / speed in floats (2D / 2 when dense)
   int64_t n_total, n_per_env, pair_begin, pair_count;
   float* tau; float* dtau; float* ltau;
   float* field; int field_kind;
@@ -469,7 +471,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
       t.valid[tid] = valid;
       t.env[tid] = valid ? int(pair / a.n_per_env) : 0;
 #pragma unroll
-      for (int i = 0; i < 2 * D; ++i) t.x[tid][i] = valid ? __ldg(a.coords + pair * 2 * D + i) : 0.f;
+      for (int i = 0; i < 2 * D; ++i) t.x[tid][i] = valid ? __ldg(a.coords + src_row(a, pair) * a.cstride + i) : 0.f;
     };
     if constexpr (!PLAN) {
       if (tid < P) {
@@ -681,8 +683,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
           }
           const float* x = ts[par].x[tid];
           if constexpr (TAIL == TC_TAIL_LOSS && ORDER == 2) {
-            const float y0 = a.alpha * __ldg(a.speed + pair * 2) + 1.0f - a.alpha;
-            const float y1 = a.alpha * __ldg(a.speed + pair * 2 + 1) + 1.0f - a.alpha;
+            const float* sp = a.speed + src_row(a, pair) * a.sstride;
+            const float y0 = a.alpha * __ldg(sp) + 1.0f - a.alpha;
+            const float y1 = a.alpha * __ldg(sp + 1) + 1.0f - a.alpha;
             a.diff[pair] = eikonal_residual<D, false>(x, tau, dtau, ltau, y0, y1, a.gamma, a.single_variant, 0.f, nullptr,
                                                       nullptr, nullptr);
           }

@@ -327,8 +327,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
         for (int c = 0; c < CGP; ++c) gy[c] = 0.f;
         if (valid) {
           float x[2 * D], y[CGP];
+          const int64_t srow = src_row(a, pair);
 #pragma unroll
-          for (int i = 0; i < 2 * D; ++i) x[i] = __ldg(a.coords + pair * 2 * D + i);
+          for (int i = 0; i < 2 * D; ++i) x[i] = __ldg(a.coords + srow * a.cstride + i);
 #pragma unroll
           for (int c = 0; c < CGP; ++c) y[c] = a.st.y13[size_t(tile) * kRows + tid * CGP + c];
           y[0] += __ldg(prm + c_b[13]);
@@ -339,8 +340,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
             dtau[i] = y[1 + i] * o.o1;
             ltau[i] = fmaf(y[1 + i] * y[1 + i], o.o2, y[1 + NG + i] * o.o1);
           }
-          const float y0 = a.alpha * __ldg(a.speed + pair * 2) + 1.0f - a.alpha;
-          const float y1 = a.alpha * __ldg(a.speed + pair * 2 + 1) + 1.0f - a.alpha;
+          const float y0 = a.alpha * __ldg(a.speed + srow * a.sstride) + 1.0f - a.alpha;
+          const float y1 = a.alpha * __ldg(a.speed + srow * a.sstride + 1) + 1.0f - a.alpha;
           float tb, dbar[NG], lbar[NG];
           eikonal_residual<D, true>(x, o.o, dtau, ltau, y0, y1, a.gamma, a.single_variant, kGradScale, &tb, dbar, lbar);
           float yb = tb * o.o1;

@@ -20,7 +20,7 @@ GRAD_EXACT, GRAD_COMPAT = 0, 1
 OP_FORWARD, OP_LOSS_FWD, OP_LOSS_BWD, OP_PLAN, OP_FIELD = 0, 1, 2, 3, 4
 
 EXPORTS = ["pntf_version", "pntf_last_error", "pntf_param_offset", "pntf_workspace_bytes", "pntf_forward",
-           "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_adamw", "pntf_plan", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end",
+           "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_loss_fwd_gather", "pntf_loss_bwd_gather", "pntf_adamw", "pntf_plan", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end",
            "pntf_tc_selftest"]
 
 _lib = None
@@ -48,6 +48,10 @@ def lib():
     L.pntf_loss_fwd.argtypes = [c_i, c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_f, c_f, c_f, c_p, c_p, c_i, c_p, c_sz, c_p]
     L.pntf_loss_bwd.argtypes = [c_i, c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_f, c_f, c_f, c_p, c_p, c_p, c_i, c_p,
                                 c_sz, c_p]
+    L.pntf_loss_fwd_gather.argtypes = [c_i, c_p, c_p, c_p, c_i64, c_p, c_i, c_i64, c_i, c_f, c_f, c_f, c_p, c_p, c_i, c_p,
+                                       c_sz, c_p]
+    L.pntf_loss_bwd_gather.argtypes = [c_i, c_p, c_p, c_p, c_i64, c_p, c_i, c_i64, c_i, c_f, c_f, c_f, c_p, c_p, c_p, c_i,
+                                       c_p, c_sz, c_p]
     c_d = ctypes.c_double
     L.pntf_adamw.argtypes = [c_p, c_p, c_p, c_p, c_p, c_i64, c_d, c_d, c_d, c_d, c_d, c_i64, c_d, c_p]
     L.pntf_plan.argtypes = [c_p, c_p, c_p, c_i64, c_i, c_f, c_f, c_i, c_i, c_p, c_p, c_i, c_p, c_sz, c_p]
@@ -173,6 +177,35 @@ def loss(variant, params, B, coords, speed, E, N, d, alpha, beta, gamma, grad_ou
         ws = workspace(workspace_bytes(OP_LOSS_BWD, E, N, d, prec, budget), dev)
         _check(lib().pntf_loss_bwd(*common, _ptr(grad_out, name="grad_out"), prec, ws.data_ptr(), ws.numel(),
                                    _stream()))
+    return loss_out, diff
+
+
+def loss_gather(variant, params, B, dataset, index, E, N, d, alpha, beta, gamma, grad_out=None, prec=PREC_FP32,
+                budget=0, diff=None, loss_out=None):
+    """loss() on the batch `dataset[index]` without materialising it: dataset[rows, 2d+2] (coords ++ speed, the
+    reference's table layout), index[E*N] int32 row numbers.  Returns (loss_out[2], diff[E*N])."""
+    dev = dataset.device
+    n = E * N
+    if dataset.dim() != 2 or dataset.shape[1] != 2 * d + 2 or not dataset.is_contiguous():
+        raise RuntimeError("dataset must be a contiguous [rows, 2d+2] tensor")
+    if index.numel() != n:
+        raise RuntimeError("index must have E*N = %d elements" % n)
+    if diff is None:
+        diff = torch.empty(n, dtype=torch.float32, device=dev)
+    if loss_out is None:
+        loss_out = torch.empty(2, dtype=torch.float32, device=dev)
+    common = (variant, _ptr(params, name="params"), _ptr(B, name="B"), _ptr(dataset, name="dataset"),
+              int(dataset.shape[0]), _ptr(index, torch.int32, "index"), E, N, d, float(alpha), float(beta), float(gamma),
+              _ptr(diff), _ptr(loss_out))
+    if grad_out is None:
+        ws = workspace(workspace_bytes(OP_LOSS_FWD, E, N, d, prec), dev)
+        _check(lib().pntf_loss_fwd_gather(*common, prec, ws.data_ptr(), ws.numel(), _stream()))
+    else:
+        if grad_out.numel() != PARAM_COUNT:
+            raise RuntimeError("grad_out must have %d elements" % PARAM_COUNT)
+        ws = workspace(workspace_bytes(OP_LOSS_BWD, E, N, d, prec, budget), dev)
+        _check(lib().pntf_loss_bwd_gather(*common, _ptr(grad_out, name="grad_out"), prec, ws.data_ptr(), ws.numel(),
+                                          _stream()))
     return loss_out, diff
 
 

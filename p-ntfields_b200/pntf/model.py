@@ -113,6 +113,14 @@ class _ModelBase:
                                 budget=self.network.stash_budget)
         return loss_out
 
+    def _loss_step_gather(self, table, index, B, E, N, alpha, beta, gamma):
+        """_loss_step on the batch table[index] (GPU-resident dataset, gather fused into the kernel loads)."""
+        fp = self.network.flat()
+        loss_out, _ = capi.loss_gather(self.variant, fp.flat, B, table, index, E, N, self.dim, alpha, beta, gamma,
+                                       grad_out=fp.grad, prec=_PREC[self.network.precision],
+                                       budget=self.network.stash_budget)
+        return loss_out
+
     def plan(self, start_goal, B=None, step=0.03, thr=0.06, max_iter=500, grad_mode=None):
         """Batched bidirectional path integration (test/gib_plan.py:53-97, test/arm_plan.py:111-158).
 

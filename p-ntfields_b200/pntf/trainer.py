@@ -7,6 +7,11 @@ gamma = 1e-3, lr clip schedule, 6 steps of 10 000 pairs (per environment) per ep
 snapshot and redo the epoch" rule.  Snapshots are device-to-device copies of the flat buffers.
 Under torch.distributed every rank processes its slice of each step's pairs and the flat gradient
 is all-reduced; the rollback decision uses the all-reduced loss and a shared random stream.
+
+Data feeding: every environment group's tables are stacked once into one
+GPU-resident [rows, 2d+2] table; a step's batch is an int32 index vector (`perm[lo:hi] + row offset` per
+environment) handed to pntf_loss_bwd_gather, so the reference's per-step `data[perm[lo:hi]]` gather, `stack`
+and `contiguous` copies (M:1053-1066) never materialise.
 """
 import random
 
@@ -39,6 +44,15 @@ def run_training(model, datas, Bs, epochs=None, log=print, inner_batch=10000, st
         n_loader = int(np.ceil(datas[0].shape[0] / inner_batch))
         norm = float(n_loader)                   # S:1083-1084
 
+    # GPU-resident tables, one per environment group (rows of the group's environments stacked)
+    tables = []
+    for grp in groups:
+        tabs = [datas[e].to(device=dev, dtype=torch.float32) for e in grp]
+        offs = [0]
+        for t in tabs:
+            offs.append(offs[-1] + t.shape[0])
+        tables.append((torch.cat(tabs).contiguous(), offs))
+
     beta, current_diff, step = 1.0, 1.0, -2000.0 / 4000.0
     snap = lambda: (fp.flat.clone(), opt.snapshot())
     current_state = snap()
@@ -68,13 +82,11 @@ def run_training(model, datas, Bs, epochs=None, log=print, inner_batch=10000, st
                 for ii in range(max(nsteps, 1)):
                     lo, hi = ii * inner_batch, min((ii + 1) * inner_batch, Ns)
                     b, e_ = shard_range(hi - lo, rank, ws)
-                    rows = [datas[e][perms[j][lo + b:lo + e_]] for j, e in enumerate(grp)]
-                    batch = torch.stack(rows)                                   # [E, n, 2d+2]
-                    n = batch.shape[1]
-                    coords = batch[:, :, :2 * d].contiguous().view(E * n, 2 * d)
-                    speed = batch[:, :, 2 * d:].contiguous().view(E * n, 2)
+                    table, offs = tables[gi]
+                    n = e_ - b
+                    index = torch.cat([perms[j][lo + b:lo + e_] + offs[j] for j in range(E)]).to(torch.int32)
                     fp.grad.zero_()
-                    loss_out = model._loss_step(coords, speed, B, E, n, alpha, beta, gamma)
+                    loss_out = model._loss_step_gather(table, index, B, E, n, alpha, beta, gamma)
                     _, loss_out = reducer(fp.grad, loss_out)
                     opt.step(grad_scale=1.0 / ws)
                     totals += loss_out

@@ -185,3 +185,44 @@ def test_tc_reference_shaped_api(capi):
     loss, loss_n, diff = ms.Loss(cu(fs["coords"]), cu(fs["speed"]), float(fs["beta"]), float(fs["gamma"]))
     assert abs(loss.item() - fs["loss"]) / abs(fs["loss"]) < 1e-2
     assert rel_err(ms.Speed2(cu(fs["coords"]), float(fs["gamma"])).cpu(), fs["speed2_pred"]) < 1e-2
+
+
+@pytest.mark.parametrize("prec_name", ["fp32", "tc"])
+@pytest.mark.parametrize("d,E,N", [(3, 1, 700), (3, 2, 333), (6, 1, 250)])
+def test_gathered_batch_equals_materialised_batch(capi, prec_name, d, E, N):
+    """pntf_loss_*_gather (batch = dataset[index], models/model_res_sigmoid_multi.py:1053-1066 fused into the kernel
+    loads) must give the same bits as the dense call on the materialised batch: same loads, same arithmetic."""
+    prec = capi.PREC_TC if prec_name == "tc" else capi.PREC_FP32
+    rs = np.random.RandomState(900 + d + E + N)
+    P = O.init_params(5)
+    flat = flat_from(P)
+    Bw = cu(0.5 * rs.normal(size=(E, d, 128)))
+    rows = 4000
+    table = np.concatenate([_pairs(rs, rows, d), rs.uniform(0.1, 1.0, size=(rows, 2)).astype(np.float32)], axis=1)
+    table = cu(table)
+    idx = torch.from_numpy(rs.randint(0, rows, size=E * N).astype(np.int32)).to(DEV)
+    batch = table[idx.long()]
+    coords, speed = batch[:, :2 * d].contiguous(), batch[:, 2 * d:].contiguous()
+    g1, g2 = torch.zeros_like(flat), torch.zeros_like(flat)
+    lo1, diff1 = capi.loss(capi.LOSS_MULTI, flat, Bw, coords, speed, E, N, d, 0.9, 1.3, 1e-3, grad_out=g1, prec=prec)
+    lo2, diff2 = capi.loss_gather(capi.LOSS_MULTI, flat, Bw, table, idx, E, N, d, 0.9, 1.3, 1e-3, grad_out=g2, prec=prec)
+    torch.cuda.synchronize()
+    assert torch.equal(diff1, diff2)
+    assert torch.equal(lo1, lo2)
+    # parameter gradients are summed with atomics: equal up to summation order
+    assert float((g1 - g2).abs().max()) <= 1e-5 * float(g1.abs().max())
+    lo3, diff3 = capi.loss_gather(capi.LOSS_MULTI, flat, Bw, table, idx, E, N, d, 0.9, 1.3, 1e-3, prec=prec)
+    torch.cuda.synchronize()
+    assert rel_err(diff3.cpu(), diff1.cpu()) < (1e-2 if prec_name == "tc" else 1e-5)
+
+
+def test_gather_rejects_bad_arguments(capi):
+    flat = torch.zeros(capi.PARAM_COUNT, device=DEV)
+    Bw = torch.zeros(1, 3, 128, device=DEV)
+    table = torch.zeros(10, 7, device=DEV)          # wrong row width for d = 3 (needs 8)
+    idx = torch.zeros(4, dtype=torch.int32, device=DEV)
+    with pytest.raises(RuntimeError):
+        capi.loss_gather(capi.LOSS_MULTI, flat, Bw, table, idx, 1, 4, 3, 1.0, 1.0, 1e-3)
+    table = torch.zeros(10, 8, device=DEV)
+    with pytest.raises(RuntimeError):
+        capi.loss_gather(capi.LOSS_MULTI, flat, Bw, table, idx[:3], 1, 4, 3, 1.0, 1.0, 1e-3)
