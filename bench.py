@@ -347,7 +347,7 @@ def run_b200(args):
 
     extra = {}
     if not args.no_plan:
-        extra["plan"] = plan_metric(model, B, d, dev)
+        extra["plan"] = plan_metric(model, B, d, dev, cpu=not args.no_cpu_baseline)
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -362,7 +362,7 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def plan_metric(model, B, d, dev, Q=65536):
+def plan_metric(model, B, d, dev, Q=65536, cpu=True):
     """Secondary metric: batched bidirectional path integration, paths/s (BASELINE configs[4]): 65 536 start/goal
     queries ~ U[-0.4,0.4]^d, reference step / threshold / cap (test/gib_plan.py:74-86, test/arm_plan.py:140-152), on
     freshly initialised weights (the trained weights of the timed steps are left alone)."""
@@ -398,7 +398,27 @@ def plan_metric(model, B, d, dev, Q=65536):
                 "alg_waypoint_GBps": steps * 2 * d * 4 / (ms * 1e-3) / 1e9,
                 "written_GBps": way.numel() * 4 / (ms * 1e-3) / 1e9,
                 "alg_tflops": steps * 2621952 / (ms * 1e-3) / 1e12 if d == 3 else None}
+    if cpu:
+        res["cpu_baseline"] = plan_cpu_baseline(q[:256].cpu(), Bq[0].cpu(), d, eta, thr, cap)
     return res
+
+
+def plan_cpu_baseline(q, Bw, d, eta, thr, cap):
+    """The reference plan loop (batched restatement of test/gib_plan.py:53-86 with per-row termination, oracle port)
+    on the host cores: 256 of the same queries, exact gradient, fp32."""
+    import torch
+    from oracle import pntf_oracle as O
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    P = O.init_params(0)
+    with torch.no_grad():
+        O.plan(P, q[:16].clone(), Bw, eta, thr, cap, "exact")          # warm-up
+        t0 = time.perf_counter()
+        way, nst = O.plan(P, q.clone(), Bw, eta, thr, cap, "exact")
+        dt = time.perf_counter() - t0
+    steps = float(nst.sum())
+    return {"paths_per_s": q.shape[0] / dt, "path_steps_per_s": steps / dt, "mean_steps": steps / q.shape[0],
+            "cores": threads, "kind": "port", "sample": "256 of the 65 536 queries, batched with per-row termination"}
 
 
 if __name__ == "__main__":

@@ -290,21 +290,16 @@ struct TcCtl {
 // all epilogue threads (converged warps): half h of the next operand tile (and its TMEM pre-loads) is complete.
 // Every thread fences its own writes; one lane per warp arrives (the barrier counts warps), which keeps the
 // mbarrier unit free for the MMA issuer's polls.
-// Forward kernel: one lane per warp arrives after __syncwarp() (the barrier counts warps): measured -3.5 ms per 1 Mi
-// pairs, the 512 per-thread arrivals compete with the MMA issuer's polls on the mbarrier unit.
+// Every epilogue thread fences its own writes and arrives (the barrier counts threads).
+// A cheaper form -- __syncwarp(), then one arrival per warp on a barrier that counts warps -- ran the forward kernel
+// 3.5 ms per 1 Mi pairs faster but dead-locked in 7 of 75 cold first launches (scripts/stress.sh; 0 of 50 with the
+// per-thread form), so it is not used (profiles/r01c_umma_microbench.md section 3).
 __device__ __forceinline__ void epi_publish(uint64_t* bar) {
-  fence_proxy_async();
-  tc_fence_before();
-  __syncwarp();
-  if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
-}
-// Reverse kernel: every thread arrives as soon as it is done (measured 2 ms faster there than the per-warp form:
-// its epilogues are longer and more skewed across lanes).
-__device__ __forceinline__ void epi_publish_each(uint64_t* bar) {
   fence_proxy_async();
   tc_fence_before();
   mbar_arrive(bar);
 }
+__device__ __forceinline__ void epi_publish_each(uint64_t* bar) { epi_publish(bar); }
 
 // MMA issue of one (contraction half kh, output half h) block: 2 stages x 4 UMMAs.  Called by the whole
 // (converged) MMA warp; one elected lane issues.
@@ -357,8 +352,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
   const int tid = threadIdx.x, warp = tid >> 5, lane_id = tid & 31;
   if (tid == 0) {
     for (int i = 0; i < S; ++i) { mbar_init(&ctl.full[i], 1); mbar_init(&ctl.empty[i], 1); }
-    mbar_init(&ctl.xr[0], kEpiWarps);
-    mbar_init(&ctl.xr[1], kEpiWarps);
+    mbar_init(&ctl.xr[0], kEpiThreads);
+    mbar_init(&ctl.xr[1], kEpiThreads);
     mbar_init(&ctl.ar[0], 1);
     mbar_init(&ctl.ar[1], 1);
     for (int i = 0; i < 4; ++i) mbar_init(&ctl.sd[i >> 1][i & 1], 1);
