@@ -278,6 +278,8 @@ struct TcCtl {
   uint64_t full[S], empty[S];   // weight ring
   uint64_t xr[2];               // operand-tile half h complete (all epilogue threads arrive)
   uint64_t ar[2];               // accumulator half h complete (tcgen05.commit)
+  uint64_t xio[2][2];           // TRAIN: operand-tile half h complete, as forwarded by the MMA issuer to the stash-store
+                                // warp; successive events alternate between two barriers (see the issuer loop)
   uint64_t sd[2][2];            // stash store of a buffer half h has finished reading shared memory; successive
                                 // events alternate between two barriers (a waiter may lag two events behind)
   uint32_t tmem_base;
@@ -290,16 +292,23 @@ struct TcCtl {
 // all epilogue threads (converged warps): half h of the next operand tile (and its TMEM pre-loads) is complete.
 // Every thread fences its own writes; one lane per warp arrives (the barrier counts warps), which keeps the
 // mbarrier unit free for the MMA issuer's polls.
-// Every epilogue thread fences its own writes and arrives (the barrier counts threads).
-// A cheaper form -- __syncwarp(), then one arrival per warp on a barrier that counts warps -- ran the forward kernel
-// 3.5 ms per 1 Mi pairs faster but dead-locked in 7 of 75 cold first launches (scripts/stress.sh; 0 of 50 with the
-// per-thread form), so it is not used (profiles/r01c_umma_microbench.md section 3).
+// Publishing an operand-tile half.  Forward kernel: every thread fences its own writes, __syncwarp(), one lane per
+// warp arrives (the barrier counts warps): 3.5 ms per 1 Mi pairs faster than 512 per-thread arrivals, which compete
+// with the MMA issuer's polls on the mbarrier unit.  (With the former stash-store protocol this faster publish exposed
+// a dead-lock on cold first launches; see the issuer loop.  scripts/stress.sh: 0 failures of 60 since.)
+// Reverse kernel: every thread arrives by itself (measured faster there: longer, more skewed epilogues).
+constexpr int kPubCount = kEpiWarps;
 __device__ __forceinline__ void epi_publish(uint64_t* bar) {
+  fence_proxy_async();
+  tc_fence_before();
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
+}
+__device__ __forceinline__ void epi_publish_each(uint64_t* bar) {
   fence_proxy_async();
   tc_fence_before();
   mbar_arrive(bar);
 }
-__device__ __forceinline__ void epi_publish_each(uint64_t* bar) { epi_publish(bar); }
 
 // MMA issue of one (contraction half kh, output half h) block: 2 stages x 4 UMMAs.  Called by the whole
 // (converged) MMA warp; one elected lane issues.
@@ -352,11 +361,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
   const int tid = threadIdx.x, warp = tid >> 5, lane_id = tid & 31;
   if (tid == 0) {
     for (int i = 0; i < S; ++i) { mbar_init(&ctl.full[i], 1); mbar_init(&ctl.empty[i], 1); }
-    mbar_init(&ctl.xr[0], kEpiThreads);
-    mbar_init(&ctl.xr[1], kEpiThreads);
+    mbar_init(&ctl.xr[0], kPubCount);
+    mbar_init(&ctl.xr[1], kPubCount);
     mbar_init(&ctl.ar[0], 1);
     mbar_init(&ctl.ar[1], 1);
     for (int i = 0; i < 4; ++i) mbar_init(&ctl.sd[i >> 1][i & 1], 1);
+    for (int i = 0; i < 4; ++i) mbar_init(&ctl.xio[i >> 1][i & 1], 1);
     mbar_init(&ctl.go, 1);
     fence_barrier_init();
   }
@@ -403,8 +413,21 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
         const uint32_t acc = tmem_base + (skip ? ACC_B : ACC_A);
 #pragma unroll 1
         for (int kh = 0; kh < KH; ++kh) {
-          if (kh == 0) { mbar_spin(&ctl.xr[0], nx0 & 1); ++nx0; }
-          else { mbar_spin(&ctl.xr[1], nx1 & 1); ++nx1; }
+          // The operand tiles are double-buffered, so the epilogue may publish X_{l+1} (other buffer) before the
+          // stash-store warp has looked at X_l: that warp can fall two events behind xr[kh], which a parity wait
+          // cannot tell from zero events behind (observed as a dead-lock on cold first launches, when the first
+          // stores into a fresh stash are slow).  The issuer sees every event in order (it is on the critical
+          // path), so it forwards them to the store warp on two alternating barriers, each of which is then at
+          // most one phase ahead of its waiter.
+          if (kh == 0) {
+            mbar_spin(&ctl.xr[0], nx0 & 1);
+            if constexpr (TRAIN) { if (lane_id == 0) mbar_arrive(&ctl.xio[0][nx0 & 1]); __syncwarp(); }
+            ++nx0;
+          } else {
+            mbar_spin(&ctl.xr[1], nx1 & 1);
+            if constexpr (TRAIN) { if (lane_id == 0) mbar_arrive(&ctl.xio[1][nx1 & 1]); __syncwarp(); }
+            ++nx1;
+          }
           tc_fence_after();
           trace_evt(a.trace, lane_id == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x, 0, l, kh);   // operand half kh seen
 #pragma unroll 1
@@ -430,8 +453,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
             const int K = c_K[l], KH = K >> 7;
 #pragma unroll 1
             for (int kh = 0; kh < KH; ++kh) {
-              if (kh == 0) { mbar_wait(&ctl.xr[0], nx0 & 1); ++nx0; }
-              else { mbar_wait(&ctl.xr[1], nx1 & 1); ++nx1; }
+#ifdef PNTF_EXP_IODELAY     // test hook (scripts/build_variants.py x:-DPNTF_EXP_IODELAY=6000): a slow store warp, as on a cold first launch
+              __nanosleep(PNTF_EXP_IODELAY);
+#endif
+              if (kh == 0) { mbar_wait(&ctl.xio[0][nx0 & 1], (nx0 >> 1) & 1); ++nx0; }
+              else { mbar_wait(&ctl.xio[1][nx1 & 1], (nx1 >> 1) & 1); ++nx1; }
               if (l == 6 && kh == 0) {
                 // encoder outputs Y5, staged by the combine epilogue in the upper half of buffer 1
                 bulk_s2g(a.st.Y5 + size_t(tile) * kHalfTileBytes, act + kTileBytes + kHalfTileBytes, kHalfTileBytes);
