@@ -34,11 +34,11 @@ UNIT = "pairs/s"
 # columns; backward = 2x forward (dX and dW)
 FWD_FLOP = {3: 14290176, 6: 27269376}
 # DRAM bytes per pair (dram__bytes_read.sum + dram__bytes_write.sum of one launch / pairs of that launch) from the
-# `ncu --set full` capture profiles/r01c_ncu_full_tc_d3.md (one 99 824-pair chunk, d = 3, tensor-core path);
+# `ncu --set full` capture profiles/r01f_ncu_full_tc_d3.md (one 99 824-pair chunk, d = 3, tensor-core path);
 # roofline.traffic = this x the pairs one launch of bench.py processes.  No capture for d = 6 / fp32: null.
-NCU_DRAM_BYTES_PER_PAIR = {("tc_forward", 3): (0.150024e9 + 9.406513e9) / 99824,
-                           ("tc_reverse", 3): (7.864236e9 + 7.723717e9) / 99824,
-                           ("tc_dw", 3): (16.357360e9 + 0.006718e9) / 99824}
+NCU_DRAM_BYTES_PER_PAIR = {("tc_forward", 3): (0.093310e9 + 9.352210e9) / 99824,
+                           ("tc_reverse", 3): (7.864198e9 + 7.724904e9) / 99824,
+                           ("tc_dw", 3): (16.357349e9 + 0.005965e9) / 99824}
 
 
 def parse():
@@ -329,7 +329,7 @@ def run_b200(args):
         traffic = per_pair * pairs_per_launch if per_pair else None
         roof = {"bound": "tensor", "kernel": top_name, "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                 "traffic": traffic,
-                "traffic_source": "profiles/r01c_ncu_full_tc_d3.md (ncu --set full, bytes per pair x pairs per launch)" if per_pair else None,
+                "traffic_source": "profiles/r01f_ncu_full_tc_d3.md (ncu --set full, bytes per pair x pairs per launch)" if per_pair else None,
                 "hbm_GBps": (per_pair * n_total * args.steps / (top_ms * 1e-3) / 1e9) if per_pair else None,
                 "hbm_peak_GBps": pk["hbm"], "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
                 "launch_ms_avg": top_ms / max(top_cnt, 1), "launches": top_cnt,
