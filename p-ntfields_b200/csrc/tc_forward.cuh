@@ -94,18 +94,29 @@ __device__ __forceinline__ float fast_sigmoid(float x) {
   return (x >= 0.f) ? inv : e * inv;
 }
 
-// hidden activation with the forward-mode rules on one unit: y[0] value, y[1..NDER] first derivatives,
-// y[1+NDER..2*NDER] diagonal second derivatives (S:641-657)
-template <int NDER, int ORDER>
+// hidden activation with the forward-mode rules on one unit (S:641-657): y[0] value, y[1..NDER] first derivatives
+// (NDER = D for an encoder endpoint, 2D for a generator pair), then the second-order columns: one per coordinate
+// (ORDER 2) or one sum per endpoint (kOrderLapSum: L <- s' sum_i dy_i^2 + s L).
+template <int D, bool GEN, int ORDER>
 __device__ __forceinline__ void act_unit(float* y, bool compat) {
+  constexpr int NDER = GEN ? 2 * D : D;
   const FastAct a = fast_act(y[0]);
   y[0] = a.a;
   const float gate = compat ? fast_sigmoid(10.0f * a.a) : a.s;
+  if constexpr (ORDER == kOrderLapSum) {
+#pragma unroll
+    for (int e = 0; e < (GEN ? 2 : 1); ++e) {
+      float q = 0.f;
+#pragma unroll
+      for (int i = 0; i < D; ++i) q = fmaf(y[1 + e * D + i], y[1 + e * D + i], q);
+      y[1 + NDER + e] = fmaf(q, a.sp, y[1 + NDER + e] * a.s);
+    }
+  }
 #pragma unroll
   for (int i = 0; i < NDER; ++i) {
     const float dy = y[1 + i];
-    if constexpr (ORDER >= 2) y[1 + NDER + i] = fmaf(dy * dy, a.sp, y[1 + NDER + i] * a.s);
-    y[1 + i] = dy * gate;
+    if constexpr (ORDER == 2) y[1 + NDER + i] = fmaf(dy * dy, a.sp, y[1 + NDER + i] * a.s);
+    if constexpr (ORDER >= 1) y[1 + i] = dy * gate;
   }
 }
 
@@ -150,11 +161,11 @@ __device__ __forceinline__ void epi_hidden_half(const EpiPos& p, int acc_col, in
     if constexpr (ENC) {
       y[0] += b;
       y[CEP] += b;
-      act_unit<C::D, C::ORDER>(y, compat);
-      act_unit<C::D, C::ORDER>(y + CEP, compat);
+      act_unit<C::D, false, C::ORDER>(y, compat);
+      act_unit<C::D, false, C::ORDER>(y + CEP, compat);
     } else {
       y[0] += b;
-      act_unit<2 * C::D, C::ORDER>(y, false);
+      act_unit<C::D, true, C::ORDER>(y, false);
     }
   }
   st_rows32(act_addr, p, f, v);
@@ -181,15 +192,22 @@ __device__ __forceinline__ void combine_unit(const float* u, const float* w, flo
     const float s1 = 1.0f - s0;
     const float q = MAXSIDE ? 10.0f * s0 * s1 : -10.0f * s0 * s1;
     const float ga = MAXSIDE ? s0 : s1, gb = MAXSIDE ? s1 : s0;   // gates of the start / goal side
+    float qa = 0.f, qb = 0.f;
 #pragma unroll
     for (int i = 0; i < D; ++i) {
       const float da = u[1 + i], db = w[1 + i];
       o[1 + i] = da * ga;
       o[1 + D + i] = db * gb;
-      if constexpr (C::ORDER >= 2) {
+      if constexpr (C::ORDER == 2) {
         o[1 + 2 * D + i] = fmaf(q * da, da, u[1 + D + i] * ga);
         o[1 + 3 * D + i] = fmaf(q * db, db, w[1 + D + i] * gb);
       }
+      qa = fmaf(da, da, qa);
+      qb = fmaf(db, db, qb);
+    }
+    if constexpr (C::LS) {   // summed second-order columns: start side, goal side
+      o[1 + 2 * D] = fmaf(q, qa, u[1 + D] * ga);
+      o[1 + 2 * D + 1] = fmaf(q, qb, w[1 + D] * gb);
     }
   }
 }
@@ -257,13 +275,20 @@ __device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>
       uc[0] = cs;
       if constexpr (C::ORDER >= 1) {
 #pragma unroll
+        float w2 = 0.f;
+#pragma unroll
         for (int i = 0; i < D; ++i) {
           us[1 + i] = w[i] * cs;
           uc[1 + i] = -w[i] * sn;
-          if constexpr (C::ORDER >= 2) {
+          if constexpr (C::ORDER == 2) {
             us[1 + D + i] = -w[i] * w[i] * sn;
             uc[1 + D + i] = -w[i] * w[i] * cs;
           }
+          w2 = fmaf(w[i], w[i], w2);
+        }
+        if constexpr (C::LS) {
+          us[1 + D] = -w2 * sn;
+          uc[1 + D] = -w2 * cs;
         }
       }
     }
@@ -693,17 +718,28 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
             const float dy = y[1 + i];
             dtau[i] = dy * o.o1;
             ltau[i] = 0.f;
-            if constexpr (ORDER >= 2) ltau[i] = fmaf(dy * dy, o.o2, y[1 + C::N1 + i] * o.o1);
+            if constexpr (ORDER == 2) ltau[i] = fmaf(dy * dy, o.o2, y[1 + C::N1 + i] * o.o1);
+          }
+          if constexpr (C::LS) {
+            // summed Laplacian columns: the per-endpoint sums go to the first slot of each endpoint (the residual
+            // only uses lap_k = sum_i ltau[k D + i])
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+              float q = 0.f;
+#pragma unroll
+              for (int i = 0; i < D; ++i) q = fmaf(y[1 + k * D + i], y[1 + k * D + i], q);
+              ltau[k * D] = fmaf(q, o.o2, y[1 + C::N1 + k] * o.o1);
+            }
           }
           if (a.tau) a.tau[pair] = tau;
           if (a.dtau)
             for (int i = 0; i < C::N1; ++i) a.dtau[pair * C::N1 + i] = dtau[i];
-          if constexpr (ORDER >= 2) {
+          if constexpr (ORDER == 2) {
             if (a.ltau)
               for (int i = 0; i < C::N1; ++i) a.ltau[pair * C::N1 + i] = ltau[i];
           }
           const float* x = ts[par].x[tid];
-          if constexpr (TAIL == TC_TAIL_LOSS && ORDER == 2) {
+          if constexpr (TAIL == TC_TAIL_LOSS && ORDER >= 2) {
             const float* sp = a.speed + src_row(a, pair) * a.sstride;
             const float y0 = a.alpha * __ldg(sp) + 1.0f - a.alpha;
             const float y1 = a.alpha * __ldg(sp + 1) + 1.0f - a.alpha;
@@ -718,7 +754,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
               field_direction<D>(x, tau, dtau, out);
               for (int i = 0; i < 2 * D; ++i) a.field[pair * 2 * D + i] = out[i];
             }
-            if constexpr (ORDER >= 2) {
+            if constexpr (ORDER == 2) {
               if (a.field_kind == 2) a.field[pair] = field_speed<D>(x, tau, dtau, ltau, a.gamma, true);
             }
           }

@@ -23,10 +23,21 @@
 namespace pntf {
 namespace tc {
 
+// ORDER: 0 value only, 1 value + first derivatives, 2 value + first + diagonal second derivatives (one column per
+// coordinate), kOrderLapSum = value + first derivatives + ONE summed second-derivative column per endpoint.
+// Model.Loss uses the Laplacian only as the per-endpoint sum lap_k = sum_i d2tau/dx_i^2 (S:905-915, M:930-944) and
+// every forward-mode rule is linear in the second-order columns (lx_i <- dx_i^2 s' + lx_i s; linear layers; combine;
+// output rule), so L <- s' sum_i dx_i^2 + s L is exact.  13 -> 9 columns per pair at d = 3 and 25 -> 15 at d = 6, where
+// a pair then takes 16 instead of 32 tile rows (twice the pairs per tile).  Used by the loss kernels only:
+// pntf_forward(LAPLACE) returns per-coordinate columns.
+constexpr int kOrderLapSum = 3;
+
 template <int D_, int ORDER_>
 struct TcCfg {
   static constexpr int D = D_, ORDER = ORDER_;
-  static constexpr int NE = ORDER * D;                              // derivative columns per endpoint
+  static constexpr bool LS = (ORDER_ == kOrderLapSum);
+  static constexpr int NL = LS ? 1 : (ORDER_ == 2 ? D_ : 0);       // second-order columns per endpoint
+  static constexpr int NE = (ORDER_ >= 1 ? D_ : 0) + NL;           // derivative columns per endpoint
   static constexpr int CE = 1 + NE;
   static constexpr int CEP = CE <= 4 ? 4 : (CE <= 8 ? 8 : 16);      // padded columns per endpoint
   static constexpr int NG = 2 * NE;                                 // derivative columns per pair

@@ -2,6 +2,7 @@
 // tcgen05 kernels.  Called from the C-ABI entry points in capi.cu.
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 
 #include "../../include/pntf_b200.h"
 #include "tc_api.cuh"
@@ -90,7 +91,19 @@ static size_t stash_tile_bytes() {
   for (int l = 0; l <= 12; ++l) s += size_t(layer_desc(l).M) * 256;
   return s + kHalfTileBytes + kRows * sizeof(float);
 }
-static int tc_tile_pairs(int d) { return d <= 3 ? TcCfg<3, 2>::P : TcCfg<6, 2>::P; }
+// Column mode of the loss kernels: summed Laplacian columns (TcCfg: kOrderLapSum, default) or one second-order column
+// per coordinate (PNTF_LOSS_COLUMNS=full; same results, kept as a cross-check).
+static int loss_order() {
+  static const int order = [] {
+    const char* e = getenv("PNTF_LOSS_COLUMNS");
+    return (e != nullptr && strcmp(e, "full") == 0) ? 2 : kOrderLapSum;
+  }();
+  return order;
+}
+static int tc_tile_pairs(int d) {
+  if (loss_order() == kOrderLapSum) return d <= 3 ? TcCfg<3, kOrderLapSum>::P : TcCfg<6, kOrderLapSum>::P;
+  return d <= 3 ? TcCfg<3, 2>::P : TcCfg<6, 2>::P;
+}
 constexpr size_t kImgBytes = ((kFwdImgBytes + kRevImgBytes + 255) / 256) * 256;
 
 size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes) {
@@ -131,11 +144,11 @@ static DwUnits make_dw_units(int sms) {
   return u;
 }
 
-template <int D>
+template <int D, int ORDER>
 static int tc_loss_bwd(int variant, const float* params, const float* B, const float* coords, const float* speed, int E,
                        int64_t N, float alpha, float beta, float gamma, float* diff, float* grad_params, uint8_t* ws,
                        size_t ws_bytes, cudaStream_t s) {
-  using C = TcCfg<D, 2>;
+  using C = TcCfg<D, ORDER>;
   const int64_t n_total = int64_t(E) * N;
   uint8_t* fimg = ws;
   uint8_t* rimg = ws + kFwdImgBytes;
@@ -145,8 +158,8 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
   const int64_t ntiles_all = (n_total + C::P - 1) / C::P;
   if (chunk_tiles > ntiles_all) chunk_tiles = ntiles_all;
   if (int rc = tc_pack(params, fimg, rimg, s)) return rc;
-  auto kf = tc_forward_kernel<D, 2, true, TC_TAIL_LOSS>;
-  auto kr = tc_reverse_kernel<D>;
+  auto kf = tc_forward_kernel<D, ORDER, true, TC_TAIL_LOSS>;
+  auto kr = tc_reverse_kernel<D, ORDER>;
   const size_t smem_f = kFwdSmem, smem_r = kRevSmem;
   const size_t smem_d = size_t(kDwStages) * kDwStageBytes + 1024;
   if (int rc = tc_set_smem(kf, smem_f)) return rc;
@@ -283,10 +296,12 @@ int tc_loss(int with_grad, int variant, const float* params, const float* B, con
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (with_grad) {
     if (int rc = tc_check_ws(workspace, workspace_bytes, kImgBytes + stash_tile_bytes())) return rc;
-    int rc = (d == 3) ? tc_loss_bwd<3>(variant, params, B, coords, speed, E, N, alpha, beta, gamma, diff, grad_params,
-                                       static_cast<uint8_t*>(workspace), workspace_bytes, s)
-                      : tc_loss_bwd<6>(variant, params, B, coords, speed, E, N, alpha, beta, gamma, diff, grad_params,
-                                       static_cast<uint8_t*>(workspace), workspace_bytes, s);
+#define PNTF_BWD(DD, OO) tc_loss_bwd<DD, OO>(variant, params, B, coords, speed, E, N, alpha, beta, gamma, diff, grad_params, \
+                                            static_cast<uint8_t*>(workspace), workspace_bytes, s)
+    int rc;
+    if (loss_order() == kOrderLapSum) rc = (d == 3) ? PNTF_BWD(3, kOrderLapSum) : PNTF_BWD(6, kOrderLapSum);
+    else rc = (d == 3) ? PNTF_BWD(3, 2) : PNTF_BWD(6, 2);
+#undef PNTF_BWD
     if (rc) return rc;
     return finalize_loss(variant, diff, int64_t(E) * N, B, E, d, beta, loss_out, s);
   }
@@ -298,7 +313,12 @@ int tc_loss(int with_grad, int variant, const float* params, const float* B, con
   apply_gather(a, d);
   a.n_total = int64_t(E) * N; a.n_per_env = N; a.pair_begin = 0; a.pair_count = a.n_total;
   a.diff = diff; a.single_variant = (variant == PNTF_LOSS_SINGLE); a.alpha = alpha; a.gamma = gamma;
-  int rc = (d == 3) ? tc_launch_forward<3, 2, false, TC_TAIL_LOSS>(a, s) : tc_launch_forward<6, 2, false, TC_TAIL_LOSS>(a, s);
+  int rc;
+  if (loss_order() == kOrderLapSum)
+    rc = (d == 3) ? tc_launch_forward<3, kOrderLapSum, false, TC_TAIL_LOSS>(a, s)
+                  : tc_launch_forward<6, kOrderLapSum, false, TC_TAIL_LOSS>(a, s);
+  else
+    rc = (d == 3) ? tc_launch_forward<3, 2, false, TC_TAIL_LOSS>(a, s) : tc_launch_forward<6, 2, false, TC_TAIL_LOSS>(a, s);
   if (rc) return rc;
   return finalize_loss(variant, diff, int64_t(E) * N, B, E, d, beta, loss_out, s);
 }

@@ -35,24 +35,44 @@ static __constant__ int c_rev_acc[kNumLayers] = {0, 1, 0, 1, 0, 0, 1, 0, 1, 0, 1
 // Adjoint of act_unit, in place on g (incoming: adjoints of the activated outputs x = (a, dx', lx') as
 // stashed by the forward pass).  With t = exp(-10 a) = 1 - s:  s'/s = 10 t,  s''/s' = 10 (1 - 2 s),
 // dy = dx'/s,  dy^2 s' = dy dx' 10 t,  ly s' = 10 t (lx' - dy^2 s').
-template <int NDER>
+template <int D, bool GEN, int ORDER>
 __device__ __forceinline__ void act_adjoint_unit(float* g, const float* x) {
+  constexpr int NDER = GEN ? 2 * D : D;
   const float t = __expf(-10.0f * x[0]);
   const float s = 1.0f - t;
   const float r = __fdividef(1.0f, fmaxf(s, 1e-6f));
   const float t10 = 10.0f * t;
   const float c2 = 10.0f * (1.0f - 2.0f * s);
   float xb = g[0] * s;
+  if constexpr (ORDER == kOrderLapSum) {
+    // summed second-order column per endpoint: L' = s' Q + s L with Q = sum_i dy_i^2 (forward: act_unit)
 #pragma unroll
-  for (int i = 0; i < NDER; ++i) {
-    const float dxp = x[1 + i], lxp = x[1 + NDER + i];
-    const float gd = g[1 + i], gl = g[1 + NDER + i];
-    const float d10 = dxp * t10;            // dy s'
-    const float u = dxp * r * d10;          // dy^2 s'
-    xb = fmaf(gd, d10, xb);
-    xb = fmaf(gl, fmaf(u, c2, t10 * (lxp - u)), xb);
-    g[1 + i] = fmaf(gd, s, 2.0f * gl * d10);
-    g[1 + NDER + i] = gl * s;
+    for (int e = 0; e < (GEN ? 2 : 1); ++e) {
+      const float gl = g[1 + NDER + e], lxp = x[1 + NDER + e];
+      float u = 0.f;                          // Q s'
+#pragma unroll
+      for (int i = 0; i < D; ++i) {
+        const float dxp = x[1 + e * D + i], gd = g[1 + e * D + i];
+        const float d10 = dxp * t10;          // dy s'
+        u = fmaf(dxp * r, d10, u);
+        xb = fmaf(gd, d10, xb);
+        g[1 + e * D + i] = fmaf(gd, s, 2.0f * gl * d10);
+      }
+      xb = fmaf(gl, fmaf(u, c2, t10 * (lxp - u)), xb);
+      g[1 + NDER + e] = gl * s;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < NDER; ++i) {
+      const float dxp = x[1 + i], lxp = x[1 + NDER + i];
+      const float gd = g[1 + i], gl = g[1 + NDER + i];
+      const float d10 = dxp * t10;            // dy s'
+      const float u = dxp * r * d10;          // dy^2 s'
+      xb = fmaf(gd, d10, xb);
+      xb = fmaf(gl, fmaf(u, c2, t10 * (lxp - u)), xb);
+      g[1 + i] = fmaf(gd, s, 2.0f * gl * d10);
+      g[1 + NDER + i] = gl * s;
+    }
   }
   g[0] = xb;
 }
@@ -88,11 +108,11 @@ __device__ __forceinline__ float epi_adjoint_half(const EpiPos& p, int in_col, i
 #pragma unroll
   for (int u = 0; u < 32 / CGP; ++u) {
     if constexpr (ENC) {
-      act_adjoint_unit<C::D>(g + u * CGP, x + u * CGP);
-      act_adjoint_unit<C::D>(g + u * CGP + CEP, x + u * CGP + CEP);
+      act_adjoint_unit<C::D, false, C::ORDER>(g + u * CGP, x + u * CGP);
+      act_adjoint_unit<C::D, false, C::ORDER>(g + u * CGP + CEP, x + u * CGP + CEP);
       db += g[u * CGP] + g[u * CGP + CEP];
     } else {
-      act_adjoint_unit<2 * C::D>(g + u * CGP, x + u * CGP);
+      act_adjoint_unit<C::D, true, C::ORDER>(g + u * CGP, x + u * CGP);
       db += g[u * CGP];
     }
   }
@@ -121,6 +141,26 @@ __device__ __forceinline__ void combine_adjoint_unit(const float* gmax, const fl
   const float q = 10.0f * s0 * s1;
   const float qp = 10.0f * q * (1.0f - 2.0f * s0);
   float ub = 0.f;
+  if constexpr (C::LS) {
+    // summed second-order columns (forward: combine_unit): lmax = [q Qa + A s0 ; q Qb + B s1], lmin = [-q Qa + A s1 ; -q Qb + B s0]
+    const float A = u[1 + D], Bq = v[1 + D];
+    const float lmax0 = gmax[1 + 2 * D], lmax1 = gmax[1 + 2 * D + 1], lmin0 = gmin[1 + 2 * D], lmin1 = gmin[1 + 2 * D + 1];
+    const float dl0 = lmax0 - lmin0, dl1 = lmax1 - lmin1;
+    float qa = 0.f, qb = 0.f;
+#pragma unroll
+    for (int i = 0; i < D; ++i) {
+      const float a = u[1 + i], b = v[1 + i];
+      const float dmax0 = gmax[1 + i], dmax1 = gmax[1 + D + i], dmin0 = gmin[1 + i], dmin1 = gmin[1 + D + i];
+      ub += q * ((dmax0 - dmin0) * a - (dmax1 - dmin1) * b);
+      qa = fmaf(a, a, qa);
+      qb = fmaf(b, b, qb);
+      ou[1 + i] = dmax0 * s0 + dmin0 * s1 + 2.0f * q * a * dl0;
+      ov[1 + i] = dmax1 * s1 + dmin1 * s0 + 2.0f * q * b * dl1;
+    }
+    ub += q * (dl0 * A - dl1 * Bq) + qp * (dl0 * qa + dl1 * qb);
+    ou[1 + D] = lmax0 * s0 + lmin0 * s1;
+    ov[1 + D] = lmax1 * s1 + lmin1 * s0;
+  } else {
 #pragma unroll
   for (int i = 0; i < D; ++i) {
     const float a = u[1 + i], b = v[1 + i], A = u[1 + D + i], Bq = v[1 + D + i];
@@ -133,6 +173,7 @@ __device__ __forceinline__ void combine_adjoint_unit(const float* gmax, const fl
     ov[1 + i] = dmax1 * s1 + dmin1 * s0 + 2.0f * q * b * dl1;
     ou[1 + D + i] = lmax0 * s0 + lmin0 * s1;
     ov[1 + D + i] = lmax1 * s1 + lmin1 * s0;
+  }
   }
   ou[0] = gmax[0] * s0 + gmin[0] * s1 + ub;
   ov[0] = gmax[0] * s1 + gmin[0] * s0 - ub;
@@ -174,9 +215,10 @@ constexpr int kRevRing = 5;
 constexpr int kNumBiasSlots = 2432;   // sum of M_l over l = 0..12: offsets c_db[l]
 static __constant__ int c_db[kNumLayers] = {0, 128, 256, 384, 512, 640, 768, 1024, 1280, 1536, 1792, 2048, 2304, 2432};
 
-template <int D>
+template <int D, int ORDER>
 __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevArgs b) {
-  using C = TcCfg<D, 2>;
+  using C = TcCfg<D, ORDER>;
+  static_assert(ORDER == 2 || ORDER == kOrderLapSum, "the loss needs second-order columns");
   constexpr int S = kRevRing;
   constexpr int CGP = C::CGP, P = C::P, NG = C::N1;
   constexpr int ACC_A = 0, ACC_B = 256;
@@ -338,13 +380,37 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
 #pragma unroll
           for (int i = 0; i < NG; ++i) {
             dtau[i] = y[1 + i] * o.o1;
-            ltau[i] = fmaf(y[1 + i] * y[1 + i], o.o2, y[1 + NG + i] * o.o1);
+            ltau[i] = 0.f;
+            if constexpr (!C::LS) ltau[i] = fmaf(y[1 + i] * y[1 + i], o.o2, y[1 + NG + i] * o.o1);
+          }
+          float qs[2] = {0.f, 0.f};
+          if constexpr (C::LS) {   // per-endpoint Laplacian sums in the first slot of each endpoint (see tc_forward tail)
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+#pragma unroll
+              for (int i = 0; i < D; ++i) qs[k] = fmaf(y[1 + k * D + i], y[1 + k * D + i], qs[k]);
+              ltau[k * D] = fmaf(qs[k], o.o2, y[1 + NG + k] * o.o1);
+            }
           }
           const float y0 = a.alpha * __ldg(a.speed + srow * a.sstride) + 1.0f - a.alpha;
           const float y1 = a.alpha * __ldg(a.speed + srow * a.sstride + 1) + 1.0f - a.alpha;
           float tb, dbar[NG], lbar[NG];
           eikonal_residual<D, true>(x, o.o, dtau, ltau, y0, y1, a.gamma, a.single_variant, kGradScale, &tb, dbar, lbar);
           float yb = tb * o.o1;
+          if constexpr (C::LS) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+              const float lb = lbar[k * D];          // d loss / d lap_k (the same for every coordinate of endpoint k)
+              yb = fmaf(lb, fmaf(qs[k], o.o3, y[1 + NG + k] * o.o2), yb);
+              gy[1 + NG + k] = lb * o.o1;
+#pragma unroll
+              for (int i = 0; i < D; ++i) {
+                const float dy = y[1 + k * D + i];
+                yb = fmaf(dbar[k * D + i] * dy, o.o2, yb);
+                gy[1 + k * D + i] = fmaf(dbar[k * D + i], o.o1, lb * 2.0f * dy * o.o2);
+              }
+            }
+          } else {
 #pragma unroll
           for (int i = 0; i < NG; ++i) {
             const float dy = y[1 + i], ly = y[1 + NG + i];
@@ -352,6 +418,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
             yb = fmaf(lbar[i], fmaf(dy * dy, o.o3, ly * o.o2), yb);
             gy[1 + i] = fmaf(dbar[i], o.o1, lbar[i] * 2.0f * dy * o.o2);
             gy[1 + NG + i] = lbar[i] * o.o1;
+          }
           }
           gy[0] = yb;
           atomicAdd(sdb + kNumBiasSlots + 128, yb);
