@@ -152,17 +152,17 @@ __device__ __forceinline__ void st_rows32(uint32_t act_addr, const EpiPos& p, in
 template <class C, bool ENC, bool PRELOAD>
 __device__ __forceinline__ void epi_hidden_half(const EpiPos& p, int acc_col, int pre_col, int f, float b, uint32_t act_addr,
                                                 bool compat) {
-  constexpr int CGP = C::CGP, CEP = C::CEP;
+  constexpr int ST = C::STRIDE, EO = C::EOFF;
   float v[32];
   tmem_ld<32>(p.tmem + acc_col + 32 * p.rq, v);
 #pragma unroll
-  for (int u = 0; u < 32 / CGP; ++u) {
-    float* y = v + u * CGP;
+  for (int u = 0; u < C::UPT; ++u) {
+    float* y = v + u * ST;
     if constexpr (ENC) {
       y[0] += b;
-      y[CEP] += b;
+      y[EO] += b;
       act_unit<C::D, false, C::ORDER>(y, compat);
-      act_unit<C::D, false, C::ORDER>(y + CEP, compat);
+      act_unit<C::D, false, C::ORDER>(y + EO, compat);
     } else {
       y[0] += b;
       act_unit<C::D, true, C::ORDER>(y, false);
@@ -179,9 +179,9 @@ __device__ __forceinline__ void epi_hidden_half(const EpiPos& p, int acc_col, in
 // each); writes the smooth-max (MAXSIDE) or smooth-min output columns (CGP) to o.
 template <class C, bool MAXSIDE>
 __device__ __forceinline__ void combine_unit(const float* u, const float* w, float* o) {
-  constexpr int CGP = C::CGP, D = C::D;
+  constexpr int D = C::D;
 #pragma unroll
-  for (int c = 0; c < CGP; ++c) o[c] = 0.f;
+  for (int c = 0; c < C::STRIDE; ++c) o[c] = 0.f;
   const float dlt = u[0] - w[0];
   const float e = __expf(-10.0f * fabsf(dlt));
   const float tail = 0.1f * __logf(1.0f + e);
@@ -218,21 +218,25 @@ __device__ __forceinline__ void combine_unit(const float* u, const float* w, flo
 // encoder outputs (bias included) to a 128-feature staging image in shared memory (training stash).
 template <class C>
 __device__ __forceinline__ void epi_combine(const EpiPos& p, int acc_col, int pre_col, float b, uint32_t act_addr, uint32_t y5_addr) {
-  constexpr int CGP = C::CGP, CEP = C::CEP;
+  constexpr int ST = C::STRIDE, EO = C::EOFF, UPT = C::UPT;
   float v[32], o[32];
   tmem_ld<32>(p.tmem + acc_col + 32 * p.rq, v);
 #pragma unroll
-  for (int u = 0; u < 32 / CGP; ++u) {
-    v[u * CGP] += b;
-    v[u * CGP + CEP] += b;
+  for (int u = 0; u < UPT; ++u) {
+    v[u * ST] += b;
+    v[u * ST + EO] += b;
+  }
+  if constexpr (UPT * ST < 32) {
+#pragma unroll
+    for (int c = UPT * ST; c < 32; ++c) o[c] = 0.f;   // unused rows of the quarter stay zero
   }
   if (y5_addr != 0) st_rows32(y5_addr, p, p.lane, v);
 #pragma unroll
-  for (int u = 0; u < 32 / CGP; ++u) combine_unit<C, true>(v + u * CGP, v + u * CGP + CEP, o + u * CGP);
+  for (int u = 0; u < UPT; ++u) combine_unit<C, true>(v + u * ST, v + u * ST + EO, o + u * ST);
   st_rows32(act_addr, p, p.lane, o);
   tmem_st<32>(p.tmem + pre_col + 32 * p.rq, o);
 #pragma unroll
-  for (int u = 0; u < 32 / CGP; ++u) combine_unit<C, false>(v + u * CGP, v + u * CGP + CEP, o + u * CGP);
+  for (int u = 0; u < UPT; ++u) combine_unit<C, false>(v + u * ST, v + u * ST + EO, o + u * ST);
   st_rows32(act_addr, p, 128 + p.lane, o);
   tmem_st<32>(p.tmem + pre_col + 128 + 32 * p.rq, o);
   tmem_st_wait();
@@ -242,7 +246,7 @@ __device__ __forceinline__ void epi_combine(const EpiPos& p, int acc_col, int pr
 // thread = (frequency k, row quarter).
 template <class C>
 __device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>& ts, uint32_t act_addr) {
-  constexpr int CGP = C::CGP, CEP = C::CEP, D = C::D;
+  constexpr int ST = C::STRIDE, EO = C::EOFF, D = C::D;
   EpiPos p;
   p.lane = threadIdx.x & 127;
   p.rq = threadIdx.x >> 7;
@@ -254,8 +258,8 @@ __device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>
 #pragma unroll
   for (int c = 0; c < 32; ++c) { vs[c] = 0.f; vc[c] = 0.f; }
 #pragma unroll
-  for (int u = 0; u < 32 / CGP; ++u) {
-    const int pr = p.rq * (32 / CGP) + u;
+  for (int u = 0; u < C::UPT; ++u) {
+    const int pr = p.rq * C::UPT + u;
     const float* Bp = a.B + int64_t(ts.env[pr]) * D * kNumFreq + k;
     float w[D];
 #pragma unroll
@@ -269,8 +273,8 @@ __device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>
       // one-step range reduction to [-pi, pi], then the fast intrinsics (abs. error ~1e-6; the tile is fp16)
       const float red = fmaf(-rintf(proj * 0.15915494f), 6.2831855f, proj);
       __sincosf(red, &sn, &cs);
-      float* us = vs + u * CGP + side * CEP;
-      float* uc = vc + u * CGP + side * CEP;
+      float* us = vs + u * ST + side * EO;
+      float* uc = vc + u * ST + side * EO;
       us[0] = sn;
       uc[0] = cs;
       if constexpr (C::ORDER >= 1) {
@@ -665,7 +669,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
           if (tid < P && active[tid]) {
             float y[CGP];
 #pragma unroll
-            for (int c = 0; c < CGP; ++c) y[c] = y13s[0][tid * CGP + c];
+            for (int c = 0; c < CGP; ++c) y[c] = y13s[0][C::pair_row(tid) + c];
             y[0] += __ldg(prm + c_b[13]);
             const ActOut o = actout_eval(y[0]);
             float dtau[C::N1], dir[2 * D];
@@ -706,9 +710,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
       if (tid < P) {
         if (ts[par].valid[tid]) {
           const int64_t pair = pair0 + tid;
-          float y[CGP];
+          float y[C::CG];
 #pragma unroll
-          for (int c = 0; c < CGP; ++c) y[c] = y13s[par][tid * CGP + c];
+          for (int c = 0; c < C::CG; ++c) y[c] = y13s[par][C::pair_row(tid) + c];
           y[0] += __ldg(prm + c_b[13]);
           const ActOut o = actout_eval(y[0]);
           const float tau = o.o;

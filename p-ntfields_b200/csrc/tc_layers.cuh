@@ -43,10 +43,20 @@ struct TcCfg {
   static constexpr int NG = 2 * NE;                                 // derivative columns per pair
   static constexpr int CG = 1 + NG;
   static constexpr int CGP = 2 * CEP;                               // padded columns per pair (>= CG)
-  static constexpr int P = 128 / CGP;                               // pairs per tile
+  // Row packing inside the 32-row quarter an epilogue thread owns: UPT pairs of STRIDE rows each; in the encoder the
+  // second endpoint of a pair starts EOFF rows after the first.  Power-of-two strides except for the d = 3 loss
+  // kernels with summed Laplacian columns: 5 rows per endpoint / 9 per pair -> stride 10, three pairs per quarter
+  // (rows 30, 31 of a quarter and row 9 of a pair stay zero), 12 instead of 8 pairs per tile.
+  static constexpr bool PACK = LS && D_ == 3;
+  static constexpr int STRIDE = PACK ? 10 : CGP;
+  static constexpr int EOFF = PACK ? 5 : CEP;
+  static constexpr int UPT = PACK ? 3 : 32 / CGP;
+  static constexpr int P = 4 * UPT;                                 // pairs per tile
   static constexpr int N1 = 2 * D;
+  __host__ __device__ static constexpr int pair_row(int t) { return (t / UPT) * 32 + (t % UPT) * STRIDE; }
   static_assert(CG <= CGP, "column padding");
   static_assert(CGP == 8 || CGP == 16 || CGP == 32, "a pair's columns must divide a 32-row quarter");
+  static_assert(EOFF >= CE && STRIDE >= 2 * EOFF && STRIDE >= CG && UPT * STRIDE <= 32, "row packing");
 };
 
 constexpr int kRows = 128;                  // rows (UMMA N) per tile

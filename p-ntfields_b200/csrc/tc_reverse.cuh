@@ -90,7 +90,7 @@ __device__ __forceinline__ void ld_rows32(uint32_t tile_addr, const EpiPos& p, i
 template <class C, bool ENC, bool PRELOAD, bool SRC13>
 __device__ __forceinline__ float epi_adjoint_half(const EpiPos& p, int in_col, int pre_col, int f, uint32_t x_addr,
                                                   uint32_t gt_addr, const float* g13s, float w13f, float& dw13) {
-  constexpr int CGP = C::CGP, CEP = C::CEP;
+  constexpr int ST = C::STRIDE, EO = C::EOFF;
   float g[32], x[32];
   if constexpr (SRC13) {
 #pragma unroll
@@ -106,14 +106,14 @@ __device__ __forceinline__ float epi_adjoint_half(const EpiPos& p, int in_col, i
   }
   float db = 0.f;
 #pragma unroll
-  for (int u = 0; u < 32 / CGP; ++u) {
+  for (int u = 0; u < C::UPT; ++u) {
     if constexpr (ENC) {
-      act_adjoint_unit<C::D, false, C::ORDER>(g + u * CGP, x + u * CGP);
-      act_adjoint_unit<C::D, false, C::ORDER>(g + u * CGP + CEP, x + u * CGP + CEP);
-      db += g[u * CGP] + g[u * CGP + CEP];
+      act_adjoint_unit<C::D, false, C::ORDER>(g + u * ST, x + u * ST);
+      act_adjoint_unit<C::D, false, C::ORDER>(g + u * ST + EO, x + u * ST + EO);
+      db += g[u * ST] + g[u * ST + EO];
     } else {
-      act_adjoint_unit<C::D, true, C::ORDER>(g + u * CGP, x + u * CGP);
-      db += g[u * CGP];
+      act_adjoint_unit<C::D, true, C::ORDER>(g + u * ST, x + u * ST);
+      db += g[u * ST];
     }
   }
   st_rows32(gt_addr, p, f, g);
@@ -129,13 +129,13 @@ __device__ __forceinline__ float epi_adjoint_half(const EpiPos& p, int in_col, i
 // endpoints (CEP columns each); writes the adjoints of the two encoder outputs to o (CGP columns).
 template <class C>
 __device__ __forceinline__ void combine_adjoint_unit(const float* gmax, const float* gmin, const float* y, float* o) {
-  constexpr int CGP = C::CGP, CEP = C::CEP, D = C::D;
+  constexpr int D = C::D;
 #pragma unroll
-  for (int c = 0; c < CGP; ++c) o[c] = 0.f;
+  for (int c = 0; c < C::STRIDE; ++c) o[c] = 0.f;
   const float* u = y;
-  const float* v = y + CEP;
+  const float* v = y + C::EOFF;
   float* ou = o;
-  float* ov = o + CEP;
+  float* ov = o + C::EOFF;
   const float s0 = fast_sigmoid(10.0f * (u[0] - v[0]));
   const float s1 = 1.0f - s0;
   const float q = 10.0f * s0 * s1;
@@ -183,20 +183,40 @@ __device__ __forceinline__ void combine_adjoint_unit(const float* gmax, const fl
 // the stashed encoder outputs Y5, writes Ybar5 (layer 5 has no activation).  Returns the bias partial sum.
 template <class C>
 __device__ __forceinline__ float epi_combine_adjoint(const EpiPos& p, int in_col, uint32_t y_addr, uint32_t gt_addr) {
-  constexpr int CGP = C::CGP, CEP = C::CEP;
+  constexpr int CGP = C::CGP, ST = C::STRIDE, EO = C::EOFF;
   float y[32];
   ld_rows32(y_addr, p, p.lane, y);
   float db = 0.f;
-  const uint32_t line = act_line_addr(gt_addr, p.lane, p.nb);
+  if constexpr (C::PACK) {
+    // packed rows (stride 10, three pairs per quarter): the adjoints of a pair are read as 16 accumulator columns
+    // starting at min(10 u, 16), the results are assembled for the whole quarter and stored at once
+    float oq[32];
 #pragma unroll
-  for (int u = 0; u < 32 / CGP; ++u) {
-    float gmax[CGP], gmin[CGP], o[CGP];
-    tmem_ld<CGP>(p.tmem + in_col + 32 * p.rq + u * CGP, gmax);
-    tmem_ld<CGP>(p.tmem + in_col + 128 + 32 * p.rq + u * CGP, gmin);
-    combine_adjoint_unit<C>(gmax, gmin, y + u * CGP, o);
-    db += o[0] + o[CEP];
+    for (int c = 0; c < 32; ++c) oq[c] = 0.f;
 #pragma unroll
-    for (int j = 0; j < CGP / 8; ++j) sts_chunk(line, p.lane & 7, p.cb + u * (CGP / 8) + j, o + 8 * j);
+    for (int u = 0; u < C::UPT; ++u) {
+      constexpr int kMaxStart = 16;
+      const int start = (u * ST < kMaxStart) ? u * ST : kMaxStart;
+      const int off = u * ST - start;
+      float gmax[16], gmin[16];
+      tmem_ld<16>(p.tmem + in_col + 32 * p.rq + start, gmax);
+      tmem_ld<16>(p.tmem + in_col + 128 + 32 * p.rq + start, gmin);
+      combine_adjoint_unit<C>(gmax + off, gmin + off, y + u * ST, oq + u * ST);
+      db += oq[u * ST] + oq[u * ST + EO];
+    }
+    st_rows32(gt_addr, p, p.lane, oq);
+  } else {
+    const uint32_t line = act_line_addr(gt_addr, p.lane, p.nb);
+#pragma unroll
+    for (int u = 0; u < 32 / CGP; ++u) {
+      float gmax[CGP], gmin[CGP], o[CGP];
+      tmem_ld<CGP>(p.tmem + in_col + 32 * p.rq + u * CGP, gmax);
+      tmem_ld<CGP>(p.tmem + in_col + 128 + 32 * p.rq + u * CGP, gmin);
+      combine_adjoint_unit<C>(gmax, gmin, y + u * CGP, o);
+      db += o[0] + o[EO];
+#pragma unroll
+      for (int j = 0; j < CGP / 8; ++j) sts_chunk(line, p.lane & 7, p.cb + u * (CGP / 8) + j, o + 8 * j);
+    }
   }
   return db;
 }
@@ -234,6 +254,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
 
   const int tid = threadIdx.x, warp = tid >> 5, lane_id = tid & 31;
   for (int i = tid; i < kNumBiasSlots + 129; i += kTcThreads) sdb[i] = 0.f;
+  if (tid < kRows) g13s[tid] = 0.f;   // rows no pair owns (packed layouts) must stay zero
   if (tid == 0) {
     for (int i = 0; i < S; ++i) { mbar_init(&ctl.full[i], 1); mbar_init(&ctl.empty[i], 1); }
     for (int h = 0; h < 2; ++h) {
@@ -373,7 +394,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
 #pragma unroll
           for (int i = 0; i < 2 * D; ++i) x[i] = __ldg(a.coords + srow * a.cstride + i);
 #pragma unroll
-          for (int c = 0; c < CGP; ++c) y[c] = a.st.y13[size_t(tile) * kRows + tid * CGP + c];
+          for (int c = 0; c < C::CG; ++c) y[c] = a.st.y13[size_t(tile) * kRows + C::pair_row(tid) + c];
           y[0] += __ldg(prm + c_b[13]);
           const ActOut o = actout_eval(y[0]);
           float dtau[NG], ltau[NG];
@@ -424,7 +445,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
           atomicAdd(sdb + kNumBiasSlots + 128, yb);
         }
 #pragma unroll
-        for (int c = 0; c < CGP; ++c) g13s[tid * CGP + c] = gy[c];
+        for (int c = 0; c < C::STRIDE; ++c) g13s[C::pair_row(tid) + c] = gy[c];
       }
       named_bar_sync(1, kEpiThreads);
       // product half ready (adjoint input, and the product is done reading operand-tile half h), the stash store of
