@@ -33,13 +33,14 @@ UNIT = "pairs/s"
 # algorithmic FLOPs per pair: 14 dense layers, 2 FLOP/MAC, all value/derivative
 # columns; backward = 2x forward (dX and dW)
 FWD_FLOP = {3: 14290176, 6: 27269376}
-# DRAM bytes per pair (dram__bytes_read.sum + dram__bytes_write.sum of one launch / pairs of that launch) from the
-# `ncu --set full` capture profiles/r01f_ncu_full_tc_d3.md (one 99 824-pair chunk, d = 3, tensor-core path);
-# roofline.traffic = this x the pairs one launch of bench.py processes.  No capture for d = 6 / fp32: null.
-NCU_DRAM_BYTES_PER_PAIR = {("tc_forward", 3): (0.093310e9 + 9.352210e9) / 99824,
-                           ("tc_reverse", 3): (7.864198e9 + 7.724904e9) / 99824,
-                           ("tc_dw", 3): (16.357349e9 + 0.005965e9) / 99824}
-
+# DRAM bytes per tile of 128 rows (dram__bytes_read.sum + dram__bytes_write.sum of one launch / tiles of that launch)
+# from the `ncu --set full` capture profiles/r01g_ncu_full_tc_d3.md (one 12 478-tile chunk, tensor-core path; the tile
+# and stash formats are the same for d = 3 and d = 6); roofline.traffic = this x the tiles one launch of bench.py
+# processes.  The loss kernels hold 12 pairs per tile at d = 3 and 8 at d = 6.
+NCU_DRAM_BYTES_PER_TILE = {"tc_forward": (0.089265e9 + 9.351010e9) / 12478,
+                           "tc_reverse": (8.077919e9 + 8.160507e9) / 12478,
+                           "tc_dw": (16.357693e9 + 0.006265e9) / 12478}
+LOSS_PAIRS_PER_TILE = {3: 12, 6: 8}
 
 def parse():
     ap = argparse.ArgumentParser()
@@ -324,17 +325,18 @@ def run_b200(args):
         flops = class_flop[top_name] * n_total * args.steps
         ach = flops / (top_ms * 1e-3) / 1e12
         peak = pk["bf16_sustained"]
-        per_pair = NCU_DRAM_BYTES_PER_PAIR.get((top_name, d))
+        per_tile = NCU_DRAM_BYTES_PER_TILE.get(top_name) if prec == "tc" else None
+        per_pair = per_tile / LOSS_PAIRS_PER_TILE[d] if per_tile else None
         pairs_per_launch = n_total * args.steps / max(top_cnt, 1)
         traffic = per_pair * pairs_per_launch if per_pair else None
         roof = {"bound": "tensor", "kernel": top_name, "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                 "traffic": traffic,
-                "traffic_source": "profiles/r01f_ncu_full_tc_d3.md (ncu --set full, bytes per pair x pairs per launch)" if per_pair else None,
+                "traffic_source": "profiles/r01g_ncu_full_tc_d3.md (ncu --set full, bytes per 128-row tile x tiles per launch)" if per_pair else None,
                 "hbm_GBps": (per_pair * n_total * args.steps / (top_ms * 1e-3) / 1e9) if per_pair else None,
                 "hbm_peak_GBps": pk["hbm"],
                 "hbm_frac": (per_pair * n_total * args.steps / (top_ms * 1e-3) / 1e9 / pk["hbm"]) if per_pair else None,
-                "note": "the training kernels move 415 KB of activation stash per pair through HBM; see DESIGN.md section 7 "
-                        "(forward 86 % of the 3.89 TB/s write-only peak, dW at the read peak)", "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
+                "note": "the training kernels move 3.37 MB of activation stash per 128-row tile (12 pairs at d=3, 8 at d=6) through "
+                        "HBM; see DESIGN.md section 7 (forward 84 % of the 3.89 TB/s write-only peak, dW at the read peak)", "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
                 "launch_ms_avg": top_ms / max(top_cnt, 1), "launches": top_cnt,
                 "share_of_step": top_ms / max(step_ms_kernels, 1e-9),
                 "alg_flop_per_pair": class_flop[top_name],
