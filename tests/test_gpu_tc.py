@@ -226,3 +226,42 @@ def test_gather_rejects_bad_arguments(capi):
     table = torch.zeros(10, 8, device=DEV)
     with pytest.raises(RuntimeError):
         capi.loss_gather(capi.LOSS_MULTI, flat, Bw, table, idx[:3], 1, 4, 3, 1.0, 1.0, 1e-3)
+
+
+@pytest.mark.parametrize("d", [3, 6])
+def test_summed_laplacian_columns_equal_per_coordinate_columns(capi, d, tmp_path):
+    """The loss kernels propagate one summed second-order column per endpoint (exact: Model.Loss only uses
+    lap_k = sum_i ltau, S:905-915 / M:930-944, and every forward-mode rule is linear in the second-order columns).
+    PNTF_LOSS_COLUMNS=full (read once per process) switches them to one column per coordinate: same loss, residuals
+    and parameter gradients up to fp16 operand rounding."""
+    import os
+    import subprocess
+    import sys
+    script = r'''
+import os, sys, numpy as np, torch
+sys.path.insert(0, os.environ["PNTF_ROOT"]); sys.path.insert(0, os.path.join(os.environ["PNTF_ROOT"], "p-ntfields_b200"))
+from pntf import capi
+from oracle import pntf_oracle as O
+d, E, N = int(sys.argv[1]), 2, 1501
+rs = np.random.RandomState(77 + d)
+P = O.init_params(9)
+flat = torch.cat([P[k].reshape(-1) for k in P]).cuda().contiguous()
+B = torch.from_numpy((0.5 * rs.normal(size=(E, d, 128))).astype(np.float32)).cuda()
+c = torch.from_numpy(rs.uniform(-0.5, 0.5, size=(E * N, 2 * d)).astype(np.float16).astype(np.float32)).cuda()
+s = torch.from_numpy(rs.uniform(0.1, 1.0, size=(E * N, 2)).astype(np.float32)).cuda()
+g = torch.zeros_like(flat)
+lo, diff = capi.loss(capi.LOSS_MULTI, flat, B, c, s, E, N, d, 0.8, 1.1, 1e-3, grad_out=g, prec=capi.PREC_TC)
+torch.cuda.synchronize()
+np.savez(sys.argv[2], lo=lo.cpu().numpy(), diff=diff.cpu().numpy(), g=g.cpu().numpy())
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = {}
+    for mode in ("sum", "full"):
+        env = dict(os.environ, PNTF_ROOT=root, PNTF_LOSS_COLUMNS=mode)
+        path = str(tmp_path / ("cols_%s.npz" % mode))
+        subprocess.run([sys.executable, "-c", script, str(d), path], check=True, env=env, timeout=300)
+        out[mode] = np.load(path)
+    a, b = out["sum"], out["full"]
+    assert abs(a["lo"][1] - b["lo"][1]) / abs(b["lo"][1]) < 1e-4
+    assert rel_err(a["diff"], b["diff"]) < 1e-2
+    assert np.abs(a["g"] - b["g"]).max() < 1e-2 * np.abs(b["g"]).max()
