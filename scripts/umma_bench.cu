@@ -25,7 +25,7 @@ struct Args {
   int nu, n, b_mn, stream, ring, reuse, nstages_img, commit_every, copy_bytes, nprod, pmode, cmode;
 };
 
-__global__ void __launch_bounds__(640, 1) bench_kernel(Args a) {
+__global__ void __launch_bounds__(128, 1) bench_kernel(Args a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* act = smem;                 // 64 KB activation tile
@@ -39,7 +39,7 @@ __global__ void __launch_bounds__(640, 1) bench_kernel(Args a) {
     fence_barrier_init();
   }
   if (warp == 0) tmem_alloc(&tmem_base_s, 512);
-  for (int i = t; i < (65536 + a.ring * kStageBytes) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+  for (int i = t; i < (65536 + a.ring * kStageBytes) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0;
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
@@ -85,8 +85,6 @@ __global__ void __launch_bounds__(640, 1) bench_kernel(Args a) {
       }
       if (lane == 0 && blockIdx.x == 0) { a.clk[202] = pw / (nst - S); a.clk[203] = pi / (nst - S); }
     }
-  } else if (warp >= 4) {
-    mbar_wait(&done, 0);   // idle epilogue threads polling an accumulator barrier
   } else if (warp == 0) {
     const uint32_t idesc = (1u << 4) | (0u << 15) | (uint32_t(a.b_mn) << 16) | (uint32_t(a.n >> 3) << 17) | (uint32_t(128 >> 4) << 24);
     const uint32_t a_hi = desc_hi(1024), b_hi = desc_hi(a.b_mn ? kActSBO : 1024);
@@ -193,24 +191,23 @@ int main() {
   cudaMalloc(&clk, 256 * sizeof(long long));
   struct Cfg { int n, b_mn, stream, ring, reuse, ctas, ce, cb, np, pm, cm; };
   std::vector<Cfg> cfgs = {
-      {128, 1, 1, 5, 1, 148, 0, 16384, 1, 0, 0}, {128, 1, 1, 5, 2, 148, 0, 16384, 1, 0, 0}, {128, 1, 0, 4, 1, 148, 1, 16384, 1, 0, 0},
+      {128, 1, 1, 5, 1, 148, 0, 16384, 1, 0, 0}, {128, 1, 1, 5, 1, 148, 0, 16384, 1, 0, 5}, {128, 1, 1, 5, 1, 148, 0, 16384, 1, 0, 6},
+      {128, 1, 1, 3, 1, 148, 0, 16384, 1, 0, 6}, {64, 1, 1, 5, 1, 148, 0, 16384, 1, 0, 6},
   };
   for (const Cfg& c : cfgs) {
     Args a{wimg, clk, 4096, c.n, c.b_mn, c.stream, c.ring, c.reuse, nst_img, c.ce, c.cb, c.np, c.pm, c.cm};
     const int smem = 65536 + 9 * kStageBytes + 1024;
     cudaFuncSetAttribute(bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     cudaMemset(clk, 0, 256 * sizeof(long long));
-    for (int nthr : {128, 640}) {
-    bench_kernel<<<c.ctas, nthr, smem>>>(a);
+    bench_kernel<<<c.ctas, 128, smem>>>(a);
     cudaError_t e = cudaDeviceSynchronize();
     std::vector<long long> h(256);
     cudaMemcpy(h.data(), clk, 256 * sizeof(long long), cudaMemcpyDeviceToHost);
     double s = 0, mx = 0;
     for (int i = 0; i < c.ctas; ++i) { s += h[i]; mx = h[i] > mx ? h[i] : mx; }
-    printf("threads=%d N=%3d b_mn=%d stream=%d ring=%d reuse=%d ctas=%3d commit_every=%d copy=%d nprod=%d pmode=%d cmode=%d : %.1f clk/UMMA (max %.1f) %s\n", nthr, c.n, c.b_mn, c.stream, c.ring, c.reuse,
+    printf("N=%3d b_mn=%d stream=%d ring=%d reuse=%d ctas=%3d commit_every=%d copy=%d nprod=%d pmode=%d cmode=%d : %.1f clk/UMMA (max %.1f) %s\n", c.n, c.b_mn, c.stream, c.ring, c.reuse,
            c.ctas, c.ce, c.cb, c.np, c.pm, c.cm, s / c.ctas / 1000.0, mx / 1000.0, cudaGetErrorString(e));
-    }
-    if (0) printf("    per stage: consumer wait %lld issue %lld | producer wait %lld issue %lld\n", h[200], h[201], h[202], h[203]);
+    printf("    per stage: consumer wait %lld issue %lld | producer wait %lld issue %lld\n", h[200], h[201], h[202], h[203]);
   }
   return 0;
 }
