@@ -353,6 +353,7 @@ def run_b200(args):
     extra = {}
     if not args.no_plan:
         extra["plan"] = plan_metric(model, B, d, dev, cpu=not args.no_cpu_baseline)
+        extra["fields"] = fields_metric(fp.flat, B, coords, d, pv)
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -365,6 +366,35 @@ def run_b200(args):
     print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def fields_metric(flat, B, coords, d, prec):
+    """Secondary metric: inference fields of SURVEY 8a row I1 (Model.TravelTimes / Speed / Speed2 / Gradient) and the three
+    forward modes on the step's pairs, pairs/s with inputs resident (CUDA events, best of 3)."""
+    import torch
+    from pntf import capi
+    n = coords.shape[0]
+    Bq = B[:1].contiguous()
+    res = {"pairs": n}
+
+    def best(f):
+        f()
+        torch.cuda.synchronize()
+        t = 1e9
+        for _ in range(3):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            f()
+            b.record()
+            torch.cuda.synchronize()
+            t = min(t, a.elapsed_time(b))
+        return n / (t * 1e-3)
+
+    for name, kind in (("travel_times", 0), ("speed", 1), ("speed2", 2), ("direction", 3)):
+        res[name + "_pairs_per_s"] = best(lambda: capi.field(kind, flat, Bq, coords, 1, n, d, gamma=1e-3, prec=prec))
+    for name, mode in (("out", capi.MODE_VALUE), ("out_grad", capi.MODE_GRAD), ("out_laplace", capi.MODE_LAPLACE)):
+        res[name + "_pairs_per_s"] = best(lambda: capi.forward(mode, flat, Bq, coords, 1, n, d, prec=prec))
+    return res
 
 
 def plan_metric(model, B, d, dev, Q=65536, cpu=True):

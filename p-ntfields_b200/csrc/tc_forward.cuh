@@ -758,7 +758,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
               field_direction<D>(x, tau, dtau, out);
               for (int i = 0; i < 2 * D; ++i) a.field[pair * 2 * D + i] = out[i];
             }
-            if constexpr (ORDER == 2) {
+            if constexpr (ORDER >= 2) {
               if (a.field_kind == 2) a.field[pair] = field_speed<D>(x, tau, dtau, ltau, a.gamma, true);
             }
           }

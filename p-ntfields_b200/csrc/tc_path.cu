@@ -246,12 +246,13 @@ int tc_field(int kind, int grad_flavour, const float* params, const float* B, co
   a.n_total = int64_t(E) * N; a.n_per_env = N; a.pair_begin = 0; a.pair_count = a.n_total;
   a.field = out; a.field_kind = kind; a.gamma = gamma;
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
+  // Speed2 uses the Laplacian only as the goal-side sum lap1 = ltau[:, dim:].sum(-1) (S:1228): summed second-order columns (TcCfg)
   const bool second = (kind == PNTF_FIELD_SPEED2);
   if (d == 3) {
-    if (second) return tc_launch_forward<3, 2, false, TC_TAIL_FIELD>(a, s);
+    if (second) return tc_launch_forward<3, kOrderLapSum, false, TC_TAIL_FIELD>(a, s);
     return tc_launch_forward<3, 1, false, TC_TAIL_FIELD>(a, s);
   }
-  if (second) return tc_launch_forward<6, 2, false, TC_TAIL_FIELD>(a, s);
+  if (second) return tc_launch_forward<6, kOrderLapSum, false, TC_TAIL_FIELD>(a, s);
   return tc_launch_forward<6, 1, false, TC_TAIL_FIELD>(a, s);
 }
 
