@@ -99,7 +99,7 @@ __device__ __forceinline__ float fast_sigmoid(float x) {
 // (ORDER 2) or one sum per endpoint (kOrderLapSum: L <- s' sum_i dy_i^2 + s L).
 template <int D, bool GEN, int ORDER>
 __device__ __forceinline__ void act_unit(float* y, bool compat) {
-  constexpr int NDER = GEN ? 2 * D : D;
+  constexpr int NDER = ORDER >= 1 ? (GEN ? 2 * D : D) : 0;
   const FastAct a = fast_act(y[0]);
   y[0] = a.a;
   const float gate = compat ? fast_sigmoid(10.0f * a.a) : a.s;
@@ -710,6 +710,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
       if (tid < P) {
         if (ts[par].valid[tid]) {
           const int64_t pair = pair0 + tid;
+          if constexpr (ORDER == 0) {
+            // value-only forward: tau, and |x1 - x0| / tau for Model.TravelTimes (S:1169-1188)
+            const float tau = actout_eval(y13s[par][C::pair_row(tid)] + __ldg(prm + c_b[13])).o;
+            if (a.tau) a.tau[pair] = tau;
+            if constexpr (TAIL == TC_TAIL_FIELD) a.field[pair] = field_travel_time<D>(ts[par].x[tid], tau);
+          } else {
           float y[C::CG];
 #pragma unroll
           for (int c = 0; c < C::CG; ++c) y[c] = y13s[par][C::pair_row(tid) + c];
@@ -761,6 +767,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
             if constexpr (ORDER >= 2) {
               if (a.field_kind == 2) a.field[pair] = field_speed<D>(x, tau, dtau, ltau, a.gamma, true);
             }
+          }
           }
         }
         // this buffer's next user is the tile after next: fetch its coordinates now (the barrier of the

@@ -47,10 +47,11 @@ struct TcCfg {
   // second endpoint of a pair starts EOFF rows after the first.  Power-of-two strides except for the d = 3 loss
   // kernels with summed Laplacian columns: 5 rows per endpoint / 9 per pair -> stride 10, three pairs per quarter
   // (rows 30, 31 of a quarter and row 9 of a pair stay zero), 12 instead of 8 pairs per tile.
+  // Value-only forward (ORDER 0: NN.out, TravelTimes, Tau): one row per endpoint, stride 2, 16 pairs per quarter.
   static constexpr bool PACK = LS && D_ == 3;
-  static constexpr int STRIDE = PACK ? 10 : CGP;
-  static constexpr int EOFF = PACK ? 5 : CEP;
-  static constexpr int UPT = PACK ? 3 : 32 / CGP;
+  static constexpr int STRIDE = PACK ? 10 : (ORDER_ == 0 ? 2 : CGP);
+  static constexpr int EOFF = PACK ? 5 : (ORDER_ == 0 ? 1 : CEP);
+  static constexpr int UPT = PACK ? 3 : 32 / STRIDE;
   static constexpr int P = 4 * UPT;                                 // pairs per tile
   static constexpr int N1 = 2 * D;
   __host__ __device__ static constexpr int pair_row(int t) { return (t / UPT) * 32 + (t % UPT) * STRIDE; }

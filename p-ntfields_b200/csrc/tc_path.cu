@@ -223,12 +223,14 @@ int tc_forward(int mode, int grad_flavour, const float* params, const float* B, 
   a.n_total = int64_t(E) * N; a.n_per_env = N; a.pair_begin = 0; a.pair_count = a.n_total;
   a.tau = tau; a.dtau = (mode >= PNTF_MODE_GRAD) ? dtau : nullptr; a.ltau = ltau;
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
-  // the value-only mode runs the first-order kernel (its extra columns are dropped)
+  // the value-only mode (NN.out) carries one tile row per endpoint: 64 pairs per 128-row tile (TcCfg ORDER 0)
   if (d == 3) {
     if (mode == PNTF_MODE_LAPLACE) return tc_launch_forward<3, 2, false, TC_TAIL_NONE>(a, s);
+    if (mode == PNTF_MODE_VALUE) return tc_launch_forward<3, 0, false, TC_TAIL_NONE>(a, s);
     return tc_launch_forward<3, 1, false, TC_TAIL_NONE>(a, s);
   }
   if (mode == PNTF_MODE_LAPLACE) return tc_launch_forward<6, 2, false, TC_TAIL_NONE>(a, s);
+  if (mode == PNTF_MODE_VALUE) return tc_launch_forward<6, 0, false, TC_TAIL_NONE>(a, s);
   return tc_launch_forward<6, 1, false, TC_TAIL_NONE>(a, s);
 }
 
@@ -248,11 +250,15 @@ int tc_field(int kind, int grad_flavour, const float* params, const float* B, co
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
   // Speed2 uses the Laplacian only as the goal-side sum lap1 = ltau[:, dim:].sum(-1) (S:1228): summed second-order columns (TcCfg)
   const bool second = (kind == PNTF_FIELD_SPEED2);
+  // TravelTimes needs tau only: value-only rows
+  const bool value = (kind == PNTF_FIELD_TRAVEL_TIME);
   if (d == 3) {
     if (second) return tc_launch_forward<3, kOrderLapSum, false, TC_TAIL_FIELD>(a, s);
+    if (value) return tc_launch_forward<3, 0, false, TC_TAIL_FIELD>(a, s);
     return tc_launch_forward<3, 1, false, TC_TAIL_FIELD>(a, s);
   }
   if (second) return tc_launch_forward<6, kOrderLapSum, false, TC_TAIL_FIELD>(a, s);
+  if (value) return tc_launch_forward<6, 0, false, TC_TAIL_FIELD>(a, s);
   return tc_launch_forward<6, 1, false, TC_TAIL_FIELD>(a, s);
 }
 

@@ -128,3 +128,22 @@ def test_plan_invariants_65536_queries(capi, setup, d, eta, thr, cap):
     # rows after the last step repeat the final position
     tail = way[idx, torch.clamp(nst.long() + 1, max=cap + 1)]
     assert torch.equal(tail, last)
+
+
+@pytest.mark.parametrize("d", [3, 6])
+def test_value_only_rows_equal_the_value_column_of_the_first_order_rows(capi, setup, d):
+    """NN.out / Model.TravelTimes run with one tile row per endpoint (64 pairs per tile); the value column of a pair
+    does not depend on which other rows share its tile, so tau must equal the first-order kernel's bit for bit, also
+    for a ragged count, and TravelTimes = |x1 - x0| / tau (S:1169-1188)."""
+    flat, data = setup
+    B, c, _ = data[d]
+    for n in (c.shape[0], 64 * 148 * 3 + 29):
+        cc = c[:n].contiguous()
+        t0, _, _ = capi.forward(capi.MODE_VALUE, flat, B, cc, 1, n, d, prec=capi.PREC_TC)
+        t1, _, _ = capi.forward(capi.MODE_GRAD, flat, B, cc, 1, n, d, prec=capi.PREC_TC)
+        tt = capi.field(capi.FIELD_TRAVEL_TIME, flat, B, cc, 1, n, d, prec=capi.PREC_TC)
+        torch.cuda.synchronize()
+        assert torch.isfinite(t0).all()
+        assert torch.equal(t0, t1)
+        want = (cc[:, d:] - cc[:, :d]).norm(dim=1) / t0
+        assert float(((tt.view(-1) - want).abs() / want.abs().clamp_min(1e-20)).max()) < 1e-5
