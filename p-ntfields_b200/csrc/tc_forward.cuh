@@ -61,7 +61,7 @@ struct TcFwdArgs {
   int max_iter;
   float* waypoints;         // [Q][max_iter+2][2D]
   int32_t* nsteps;          // [Q]
-  int* tile_counter;        // zeroed by the host: tiles of queries are handed out dynamically
+  int* tile_counter;        // zeroed by the host: path queries are handed out to free tile slots dynamically
 };
 
 // debug time stamps: slot layout [role][layer][event]
@@ -278,7 +278,6 @@ __device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>
       us[0] = sn;
       uc[0] = cs;
       if constexpr (C::ORDER >= 1) {
-#pragma unroll
         float w2 = 0.f;
 #pragma unroll
         for (int i = 0; i < D; ++i) {
@@ -634,67 +633,106 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     if constexpr (PLAN) {
       // ---- batched bidirectional path integration: per tile of P queries iterate XP += eta * Gradient(XP) until the
       // endpoints of every query met (|x1 - x0| <= thr) or max_iter + 1 steps were taken (test/gib_plan.py:74-86)
+      // A tile is P query slots; a slot whose query finished takes the next unstarted query from a global counter before
+      // the next pass, so every pass carries P live queries until the queue runs dry (step counts differ widely between
+      // queries; rows of a tile are independent, so a query's waypoints do not depend on its tile mates).
+      struct Done { int64_t q; int steps; float x[2 * D]; };
       __shared__ int active[P];
       __shared__ int steps_s[P];
+      __shared__ int64_t qid[P];
+      __shared__ Done done[P];
+      __shared__ int ndone[2];
       const int64_t wstride = int64_t(a.max_iter + 2) * 2 * D;
+      const int nrow = a.max_iter + 2;
       TcTile<C>& t0 = ts[0];
-      for (;;) {
-        if (tid == 0) ctl.next_tile = atomicAdd(a.tile_counter, 1);
-        named_bar_sync(1, kEpiThreads);
-        const int64_t tile = ctl.next_tile;
-        if (tile >= ntiles) break;
-        const int64_t pair0 = a.pair_begin + tile * P;
-        if (tid < P) {
-          load_tile(tile, t0);
-          float d2 = 0.f;
-#pragma unroll
-          for (int i = 0; i < D; ++i) { const float dv = t0.x[tid][D + i] - t0.x[tid][i]; d2 = fmaf(dv, dv, d2); }
-          active[tid] = t0.valid[tid] && sqrtf(d2) > a.thr;
-          steps_s[tid] = 0;
-          if (t0.valid[tid])
-            for (int i = 0; i < 2 * D; ++i) a.waypoints[(pair0 + tid) * wstride + i] = t0.x[tid][i];
-        }
-        named_bar_sync(1, kEpiThreads);
+      if (tid < P) active[tid] = 0;
+      if (tid == 0) { ndone[0] = 0; ndone[1] = 0; }
 #pragma unroll 1
-        for (int it = 1; it <= a.max_iter + 1; ++it) {
-          int any = 0;
+      for (uint32_t round = 0;; ++round) {
+        if (tid < P && !active[tid]) {
+          // refill this slot
+          for (;;) {
+            const int64_t q = int64_t(atomicAdd(a.tile_counter, 1));
+            if (q >= a.pair_count) {
+              t0.valid[tid] = 0;
+              t0.env[tid] = 0;
 #pragma unroll
-          for (int q = 0; q < P; ++q) any |= active[q];
-          if (!any) break;
-          if (tid == 0) {
-            ctl.more = 1;
-            mbar_arrive(&ctl.go);
-          }
-          pass(false, 0, false);
-          if (tid < P && active[tid]) {
-            float y[CGP];
-#pragma unroll
-            for (int c = 0; c < CGP; ++c) y[c] = y13s[0][C::pair_row(tid) + c];
-            y[0] += __ldg(prm + c_b[13]);
-            const ActOut o = actout_eval(y[0]);
-            float dtau[C::N1], dir[2 * D];
-#pragma unroll
-            for (int i = 0; i < C::N1; ++i) dtau[i] = y[1 + i] * o.o1;
-            field_direction<D>(t0.x[tid], o.o, dtau, dir);
+              for (int i = 0; i < 2 * D; ++i) t0.x[tid][i] = 0.f;
+              break;
+            }
+            const int64_t pair = a.pair_begin + q;
+            float* w = a.waypoints + pair * wstride;
             float d2 = 0.f;
 #pragma unroll
-            for (int i = 0; i < 2 * D; ++i) t0.x[tid][i] = fmaf(a.eta, dir[i], t0.x[tid][i]);
+            for (int i = 0; i < 2 * D; ++i) {
+              t0.x[tid][i] = __ldg(a.coords + src_row(a, pair) * a.cstride + i);
+              w[i] = t0.x[tid][i];
+            }
 #pragma unroll
             for (int i = 0; i < D; ++i) { const float dv = t0.x[tid][D + i] - t0.x[tid][i]; d2 = fmaf(dv, dv, d2); }
-            steps_s[tid] = it;
-            for (int i = 0; i < 2 * D; ++i) a.waypoints[(pair0 + tid) * wstride + int64_t(it) * 2 * D + i] = t0.x[tid][i];
-            if (!(sqrtf(d2) > a.thr)) active[tid] = 0;
+            if (sqrtf(d2) > a.thr) {
+              t0.valid[tid] = 1;
+              t0.env[tid] = int(pair / a.n_per_env);
+              qid[tid] = pair;
+              steps_s[tid] = 0;
+              active[tid] = 1;
+              break;
+            }
+            // the endpoints already meet: no step; every row repeats the query
+            for (int r = 1; r < nrow; ++r)
+              for (int i = 0; i < 2 * D; ++i) w[int64_t(r) * 2 * D + i] = t0.x[tid][i];
+            a.nsteps[pair] = 0;
           }
-          named_bar_sync(1, kEpiThreads);
         }
-        // rows after the last step repeat the final position
-        for (int q = 0; q < P; ++q) {
-          if (!t0.valid[q]) continue;
-          const int64_t base = (pair0 + q) * wstride;
-          const int first_e = (steps_s[q] + 1) * 2 * D, last_e = (a.max_iter + 2) * 2 * D;
-          for (int e = first_e + tid; e < last_e; e += kEpiThreads) a.waypoints[base + e] = t0.x[q][e % (2 * D)];
+        named_bar_sync(1, kEpiThreads);
+        int any = 0;
+#pragma unroll
+        for (int q = 0; q < P; ++q) any |= active[q];
+        if (!any) break;
+        if (tid == 0) {
+          ctl.more = 1;
+          mbar_arrive(&ctl.go);
         }
-        if (tid < P && t0.valid[tid]) a.nsteps[pair0 + tid] = steps_s[tid];
+        pass(false, 0, false);
+        if (tid < P && active[tid]) {
+          float y[CGP];
+#pragma unroll
+          for (int c = 0; c < CGP; ++c) y[c] = y13s[0][C::pair_row(tid) + c];
+          y[0] += __ldg(prm + c_b[13]);
+          const ActOut o = actout_eval(y[0]);
+          float dtau[C::N1], dir[2 * D];
+#pragma unroll
+          for (int i = 0; i < C::N1; ++i) dtau[i] = y[1 + i] * o.o1;
+          field_direction<D>(t0.x[tid], o.o, dtau, dir);
+          float d2 = 0.f;
+#pragma unroll
+          for (int i = 0; i < 2 * D; ++i) t0.x[tid][i] = fmaf(a.eta, dir[i], t0.x[tid][i]);
+#pragma unroll
+          for (int i = 0; i < D; ++i) { const float dv = t0.x[tid][D + i] - t0.x[tid][i]; d2 = fmaf(dv, dv, d2); }
+          const int it = ++steps_s[tid];
+          float* w = a.waypoints + qid[tid] * wstride + int64_t(it) * 2 * D;
+          for (int i = 0; i < 2 * D; ++i) w[i] = t0.x[tid][i];
+          if (!(sqrtf(d2) > a.thr) || it == a.max_iter + 1) {
+            active[tid] = 0;
+            Done& r = done[atomicAdd(&ndone[round & 1], 1)];
+            r.q = qid[tid];
+            r.steps = it;
+#pragma unroll
+            for (int i = 0; i < 2 * D; ++i) r.x[i] = t0.x[tid][i];
+          }
+        }
+        named_bar_sync(1, kEpiThreads);
+        // rows after the last step of the queries that finished in this round repeat the final position (all threads);
+        // the other counter was last read in the previous round, before this round's pass
+        const int nd = ndone[round & 1];
+        if (tid == 0) ndone[(round + 1) & 1] = 0;
+        for (int k = 0; k < nd; ++k) {
+          const Done& r = done[k];
+          float* w = a.waypoints + r.q * wstride;
+          const int first_e = (r.steps + 1) * 2 * D, last_e = nrow * 2 * D;
+          for (int e = first_e + tid; e < last_e; e += kEpiThreads) w[e] = r.x[e % (2 * D)];
+          if (tid == 0) a.nsteps[r.q] = r.steps;
+        }
       }
       if (tid == 0) {
         ctl.more = 0;

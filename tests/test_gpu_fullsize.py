@@ -147,3 +147,27 @@ def test_value_only_rows_equal_the_value_column_of_the_first_order_rows(capi, se
         assert torch.equal(t0, t1)
         want = (cc[:, d:] - cc[:, :d]).norm(dim=1) / t0
         assert float(((tt.view(-1) - want).abs() / want.abs().clamp_min(1e-20)).max()) < 1e-5
+
+
+@pytest.mark.parametrize("d,eta,thr,cap", [(3, 0.03, 0.06, 20), (6, 0.015, 0.03, 45)])
+def test_plan_does_not_depend_on_slot_scheduling(capi, setup, d, eta, thr, cap):
+    """Finished queries hand their tile slot to the next unstarted query (dynamic refill), so which queries share a
+    tile differs from run to run and with the batch; a query's rows are independent of its tile mates, so its
+    waypoints must be bit-identical when it is planned alone in a small batch, in a permuted batch, or among 65 536;
+    the low cap also exercises the step-cap exit next to the met exit."""
+    from pntf import synth
+    flat, data = setup
+    B = data[d][0]
+    Q = 65536
+    q = synth.sample_queries(Q, d, DEV)
+    q[5, d:] = q[5, :d] + 0.1 * thr                                      # already met: zero steps
+    way, nst = capi.plan(flat, B, q, d, eta, thr, cap, capi.GRAD_EXACT, prec=capi.PREC_TC)
+    sub = torch.arange(0, Q, 97, device=DEV)
+    way_s, nst_s = capi.plan(flat, B, q[sub].contiguous(), d, eta, thr, cap, capi.GRAD_EXACT, prec=capi.PREC_TC)
+    perm = torch.randperm(Q, device=DEV, generator=torch.Generator(device=DEV).manual_seed(3))
+    way_p, nst_p = capi.plan(flat, B, q[perm].contiguous(), d, eta, thr, cap, capi.GRAD_EXACT, prec=capi.PREC_TC)
+    torch.cuda.synchronize()
+    assert int(nst[5]) == 0 and torch.equal(way[5], q[5].expand(cap + 2, 2 * d))
+    assert int(nst.max()) == cap + 1 and int((nst <= cap).sum()) > 0     # both exits taken
+    assert torch.equal(nst_s, nst[sub]) and torch.equal(way_s, way[sub])
+    assert torch.equal(nst_p, nst[perm]) and torch.equal(way_p, way[perm])
