@@ -354,6 +354,8 @@ def run_b200(args):
     if not args.no_plan:
         extra["plan"] = plan_metric(model, B, d, dev, cpu=not args.no_cpu_baseline)
         extra["fields"] = fields_metric(fp.flat, B, coords, d, pv)
+        if d == 3:
+            extra["speed_sampling"] = speed_sampling_metric(dev, cpu=not args.no_cpu_baseline)
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -366,6 +368,64 @@ def run_b200(args):
     print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def speed_sampling_metric(dev, cpu=True, N=1 << 20, levels=6):
+    """Secondary metric (dataprocessing/speed_sampling_gpu.py:325-421): unsigned point-to-mesh
+    distance queries/s for 1 Mi points against a synthetic scene of three boxes subdivided to 147 456 triangles, and
+    sampled pairs/s of the whole rejection sampler (random draws, two distance queries, filtering) in the Gibson band."""
+    import numpy as np
+    import torch
+    from oracle import mesh_oracle as MO
+    from pntf import capi, speed_sampling as SS
+    boxes = [((-0.3, -0.3, -0.3), (-0.05, 0.0, 0.1)), ((0.1, -0.2, -0.4), (0.4, 0.35, -0.1)),
+             ((-0.1, 0.2, 0.15), (0.3, 0.45, 0.4))]
+    tri = np.concatenate([MO.box_mesh(lo, hi) for lo, hi in boxes])
+    for _ in range(levels):
+        a, b, c = tri[:, 0], tri[:, 1], tri[:, 2]
+        ab, bc, ca = (a + b) / 2, (b + c) / 2, (c + a) / 2
+        tri = np.concatenate([np.stack(t, 1) for t in ((a, ab, ca), (ab, b, bc), (ca, bc, c), (ab, bc, ca))])
+    g = torch.Generator(device=dev).manual_seed(11)
+    t = torch.tensor(tri, dtype=torch.float32, device=dev)
+    t = t[torch.randperm(t.shape[0], device=dev, generator=g)].contiguous()       # mesh files are not spatially sorted
+    pts = torch.rand(N, 3, device=dev, generator=g) - 0.5
+    mesh = SS.ObstacleMesh(t.unsqueeze(0))
+
+    def timed(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps * 1e-3
+
+    order = SS._morton_order(pts)
+    ps = pts[order].contiguous()
+    sec_kernel = timed(lambda: capi.mesh_distance(mesh.triangles, ps))
+    sec_api = timed(lambda: mesh.distance(pts))
+    sec_unsorted = timed(lambda: capi.mesh_distance(t, pts), reps=1)
+    offset, margin = SS.band_for_task("gibson")
+    want = 100000
+    torch.manual_seed(5)
+    X, Y = [], []
+    sec_sampler = timed(lambda: SS.point_append_list(X, Y, mesh, want, 3, offset, margin), reps=1)
+    res = {"triangles": int(t.shape[0]), "points": N,
+           "distance_queries_per_s": N / sec_kernel, "distance_queries_per_s_with_host_sort": N / sec_api,
+           "distance_queries_per_s_unsorted_inputs": N / sec_unsorted,
+           "brute_force_equivalent_pair_tests_per_s": N * float(t.shape[0]) / sec_kernel,
+           "sampler_pairs_per_s": want / sec_sampler, "sampler_pairs": want, "band": [offset, margin]}
+    if cpu:
+        n = 256
+        p = pts[:n].cpu().numpy()
+        t0 = time.perf_counter()
+        MO.point_obstacle_distance(p, tri)
+        dt = time.perf_counter() - t0
+        res["cpu_baseline"] = {"distance_queries_per_s": n / dt, "kind": "port", "cores": 1,
+                               "sample": "%d of the points, brute force over all triangles in numpy float64" % n}
+    return res
 
 
 def fields_metric(flat, B, coords, d, prec):

@@ -126,6 +126,17 @@ int pntf_plan(const float* params, const float* B, const float* start_goal, int6
               float* waypoints, int32_t* nsteps, int prec,
               void* workspace, size_t workspace_bytes, void* stream);
 
+/* Ground-truth speed sampling: unsigned distance from N query points [N,3] to a triangle soup
+ * triangles[M,3,3] and, when speed != NULL, speed = clip(distance, offset, margin) / margin.
+ * Replaces dataprocessing/speed_sampling_gpu.py:325-336 (point_obstacle_distance: sqrt of the squared distance of the
+ * third-party bvh_distance_queries.BVH) and the clipping of :415-419 (point_rand_sample_bound_points).  Exact
+ * point-triangle distances (closest point by Voronoi region), minimum over the mesh; results do not depend on the
+ * order of triangles or points, spatially sorted inputs run faster.  Workspace: pntf_mesh_workspace_bytes(M). */
+size_t pntf_mesh_workspace_bytes(int64_t M);
+int pntf_mesh_distance(const float* triangles, int64_t M, const float* points, int64_t N, float* distance,
+                       float offset, float margin, float* speed, void* workspace, size_t workspace_bytes,
+                       void* stream);
+
 /* Measurement aid for bench.py: between begin and end every kernel (group) the library launches is
  * bracketed by CUDA events on its stream; end synchronises on them and returns, per kernel class
  * (0 pack, 1 forward, 2 reverse, 3 dW, 4 loss-finalize, 5 adamw, 6 plan, 7 tc-forward, 8 tc-reverse,

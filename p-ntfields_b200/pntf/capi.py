@@ -21,7 +21,7 @@ OP_FORWARD, OP_LOSS_FWD, OP_LOSS_BWD, OP_PLAN, OP_FIELD = 0, 1, 2, 3, 4
 
 EXPORTS = ["pntf_version", "pntf_last_error", "pntf_param_offset", "pntf_workspace_bytes", "pntf_forward",
            "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_loss_fwd_gather", "pntf_loss_bwd_gather", "pntf_adamw", "pntf_plan", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end",
-           "pntf_tc_selftest"]
+           "pntf_tc_selftest", "pntf_mesh_workspace_bytes", "pntf_mesh_distance"]
 
 _lib = None
 
@@ -56,6 +56,9 @@ def lib():
     L.pntf_adamw.argtypes = [c_p, c_p, c_p, c_p, c_p, c_i64, c_d, c_d, c_d, c_d, c_d, c_i64, c_d, c_p]
     L.pntf_plan.argtypes = [c_p, c_p, c_p, c_i64, c_i, c_f, c_f, c_i, c_i, c_p, c_p, c_i, c_p, c_sz, c_p]
     L.pntf_tc_selftest.argtypes = [c_p, c_p, c_p, c_p, c_p]
+    L.pntf_mesh_workspace_bytes.restype = c_sz
+    L.pntf_mesh_workspace_bytes.argtypes = [c_i64]
+    L.pntf_mesh_distance.argtypes = [c_p, c_i64, c_p, c_i64, c_p, c_f, c_f, c_p, c_p, c_sz, c_p]
     _lib = L
     return L
 
@@ -227,6 +230,20 @@ def plan(params, B, start_goal, d, eta, thr, max_iter, grad_flavour=GRAD_EXACT, 
                            float(eta), float(thr), int(max_iter), grad_flavour, _ptr(way),
                            _ptr(nsteps, torch.int32), prec, ws.data_ptr(), ws.numel(), _stream()))
     return way, nsteps
+
+
+def mesh_distance(triangles, points, offset=None, margin=None):
+    """Unsigned distance of points [N,3] to the triangle soup triangles[M,3,3] (dataprocessing/speed_sampling_gpu.py:
+    325-336); with offset / margin also speed = clip(distance, offset, margin) / margin (:415-419)."""
+    dev = points.device
+    M, N = triangles.shape[0], points.shape[0]
+    dist = torch.empty(N, dtype=torch.float32, device=dev)
+    speed = torch.empty(N, dtype=torch.float32, device=dev) if margin is not None else None
+    ws = workspace(lib().pntf_mesh_workspace_bytes(M), dev)
+    _check(lib().pntf_mesh_distance(_ptr(triangles, name="triangles"), M, _ptr(points, name="points"), N, _ptr(dist),
+                                    float(offset or 0.0), float(margin or 0.0),
+                                    _ptr(speed) if speed is not None else None, ws.data_ptr(), ws.numel(), _stream()))
+    return (dist, speed) if speed is not None else dist
 
 
 def tc_selftest(W, X, C):
