@@ -73,7 +73,6 @@ int sm_count() {
   return n;
 }
 
-static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 constexpr size_t kPackedBytes = ((size_t(kPackedCount) * 4 + 255) / 256) * 256;
 
 static int tile_pairs(int d) { return d <= 3 ? 8 : 4; }

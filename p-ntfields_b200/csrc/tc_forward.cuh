@@ -314,7 +314,6 @@ struct TcCtl {
   // TC_TAIL_PLAN: the number of passes is data dependent; an epilogue thread announces every pass
   uint64_t go;                  // completes once per announcement
   volatile int more;            // 1 = another pass follows, 0 = the CTA is done
-  volatile int next_tile;
 };
 
 // all epilogue threads (converged warps): half h of the next operand tile (and its TMEM pre-loads) is complete.

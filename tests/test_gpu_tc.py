@@ -265,3 +265,24 @@ np.savez(sys.argv[2], lo=lo.cpu().numpy(), diff=diff.cpu().numpy(), g=g.cpu().nu
     assert abs(a["lo"][1] - b["lo"][1]) / abs(b["lo"][1]) < 1e-4
     assert rel_err(a["diff"], b["diff"]) < 1e-2
     assert np.abs(a["g"] - b["g"]).max() < 1e-2 * np.abs(b["g"]).max()
+
+
+@pytest.mark.parametrize("d,E,N", [(3, 2, 777), (6, 3, 131)])
+def test_tc_value_only_rows_multi_env(capi, d, E, N):
+    """Value-only rows (64 pairs per tile) with several environments in one tile: every pair must pick its own
+    environment's Fourier matrix (M:199-213); tau equals the first-order kernel's value column bit for bit."""
+    rs = np.random.RandomState(77 + d)
+    P = O.init_params(4)
+    Bw = (0.5 * rs.normal(size=(E, d, 128))).astype(np.float32)
+    c = np.concatenate([_pairs(rs, N, d) for _ in range(E)])
+    flat = flat_from(P)
+    t0, _, _ = capi.forward(capi.MODE_VALUE, flat, cu(Bw), cu(c), E, N, d, prec=capi.PREC_TC)
+    t1, _, _ = capi.forward(capi.MODE_GRAD, flat, cu(Bw), cu(c), E, N, d, prec=capi.PREC_TC)
+    assert torch.equal(t0, t1)
+    with torch.no_grad():
+        for e in range(E):
+            tau, _, _ = O.forward(P, T(c[e * N:(e + 1) * N]), T(Bw[e]), 1)
+            assert pointwise_rel(t0[e * N:(e + 1) * N].cpu(), tau[:, 0]) < 1e-3
+    tt = capi.field(capi.FIELD_TRAVEL_TIME, flat, cu(Bw), cu(c), E, N, d, prec=capi.PREC_TC)
+    want = np.linalg.norm(c[:, d:] - c[:, :d], axis=1) / t0.cpu().numpy()
+    assert np.abs(tt.cpu().numpy().reshape(-1) - want).max() / np.abs(want).max() < 1e-5
