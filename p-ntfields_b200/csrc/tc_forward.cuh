@@ -647,12 +647,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
       if (tid < P) active[tid] = 0;
       if (tid == 0) { ndone[0] = 0; ndone[1] = 0; }
 #pragma unroll 1
+      bool drained = false;   // the query counter ran past the end: this slot stays empty
       for (uint32_t round = 0;; ++round) {
-        if (tid < P && !active[tid]) {
+        if (tid < P && !active[tid] && !drained) {
           // refill this slot
           for (;;) {
             const int64_t q = int64_t(atomicAdd(a.tile_counter, 1));
             if (q >= a.pair_count) {
+              drained = true;
               t0.valid[tid] = 0;
               t0.env[tid] = 0;
 #pragma unroll
