@@ -374,20 +374,10 @@ def speed_sampling_metric(dev, cpu=True, N=1 << 20, levels=6):
     """Secondary metric (dataprocessing/speed_sampling_gpu.py:325-421): unsigned point-to-mesh
     distance queries/s for 1 Mi points against a synthetic scene of three boxes subdivided to 147 456 triangles, and
     sampled pairs/s of the whole rejection sampler (random draws, two distance queries, filtering) in the Gibson band."""
-    import numpy as np
     import torch
-    from oracle import mesh_oracle as MO
-    from pntf import capi, speed_sampling as SS
-    boxes = [((-0.3, -0.3, -0.3), (-0.05, 0.0, 0.1)), ((0.1, -0.2, -0.4), (0.4, 0.35, -0.1)),
-             ((-0.1, 0.2, 0.15), (0.3, 0.45, 0.4))]
-    tri = np.concatenate([MO.box_mesh(lo, hi) for lo, hi in boxes])
-    for _ in range(levels):
-        a, b, c = tri[:, 0], tri[:, 1], tri[:, 2]
-        ab, bc, ca = (a + b) / 2, (b + c) / 2, (c + a) / 2
-        tri = np.concatenate([np.stack(t, 1) for t in ((a, ab, ca), (ab, b, bc), (ca, bc, c), (ab, bc, ca))])
+    from pntf import capi, synth, speed_sampling as SS
+    t = synth.box_scene_mesh(dev, levels)                                          # shuffled: mesh files are not sorted
     g = torch.Generator(device=dev).manual_seed(11)
-    t = torch.tensor(tri, dtype=torch.float32, device=dev)
-    t = t[torch.randperm(t.shape[0], device=dev, generator=g)].contiguous()       # mesh files are not spatially sorted
     pts = torch.rand(N, 3, device=dev, generator=g) - 0.5
     mesh = SS.ObstacleMesh(t.unsqueeze(0))
 
@@ -418,8 +408,10 @@ def speed_sampling_metric(dev, cpu=True, N=1 << 20, levels=6):
            "brute_force_equivalent_pair_tests_per_s": N * float(t.shape[0]) / sec_kernel,
            "sampler_pairs_per_s": want / sec_sampler, "sampler_pairs": want, "band": [offset, margin]}
     if cpu:
+        from oracle import mesh_oracle as MO                                       # CPU leg only
         n = 256
         p = pts[:n].cpu().numpy()
+        tri = t.cpu().numpy()
         t0 = time.perf_counter()
         MO.point_obstacle_distance(p, tri)
         dt = time.perf_counter() - t0

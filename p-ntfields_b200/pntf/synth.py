@@ -72,3 +72,27 @@ def sample_queries(Q, d, device, seed=3):
     """start/goal ~ U[-0.4,0.4]^d."""
     g = torch.Generator().manual_seed(seed)
     return ((torch.rand(Q, 2 * d, generator=g) - 0.5) * 0.8).to(device)
+
+
+BOX_SCENE = (((-0.3, -0.3, -0.3), (-0.05, 0.0, 0.1)), ((0.1, -0.2, -0.4), (0.4, 0.35, -0.1)),
+             ((-0.1, 0.2, 0.15), (0.3, 0.45, 0.4)))
+
+
+def box_scene_mesh(device, levels=6, boxes=BOX_SCENE, shuffle_seed=11):
+    """Synthetic obstacle mesh for the speed-sampling benchmark: the surfaces of a few axis-aligned boxes, every
+    triangle split into four `levels` times (36 * 4**levels triangles), in shuffled order as a mesh file would be.
+    Returns triangles [M,3,3] fp32 on `device`."""
+    quads = ((0, 1, 3, 2), (4, 6, 7, 5), (0, 4, 5, 1), (2, 3, 7, 6), (0, 2, 6, 4), (1, 5, 7, 3))
+    tris = []
+    for lo, hi in boxes:
+        v = torch.tensor([[(hi if (k >> i) & 1 else lo)[i] for i in range(3)] for k in range(8)], dtype=torch.float64)
+        for q in quads:
+            tris.append(v[[q[0], q[1], q[2]]])
+            tris.append(v[[q[0], q[2], q[3]]])
+    t = torch.stack(tris).to(device)
+    for _ in range(levels):
+        a, b, c = t[:, 0], t[:, 1], t[:, 2]
+        ab, bc, ca = (a + b) / 2, (b + c) / 2, (c + a) / 2
+        t = torch.cat([torch.stack(x, 1) for x in ((a, ab, ca), (ab, b, bc), (ca, bc, c), (ab, bc, ca))])
+    g = torch.Generator(device=device).manual_seed(shuffle_seed)
+    return t[torch.randperm(t.shape[0], device=device, generator=g)].to(torch.float32).contiguous()
