@@ -343,6 +343,9 @@ __device__ __forceinline__ void epi_publish_each(uint64_t* bar) {
 // warp 100-250 clk and the UMMA queue is shallow, so the per-stage poll + commit keeps the pipe at ~110-130 clk per
 // UMMA (floor 64).  A ring of three 32 KB blocks (one poll per 8 UMMAs, same smem look-ahead) was tried and was
 // 4 ms per 1 Mi pairs SLOWER in the training forward (coarser slot release), so the 16 KB stages stay.
+#ifndef PNTF_NO_LOOKAHEAD
+#define PNTF_LOOKAHEAD 1   // +4-5 % on the no-stash forward (profiles/r01m_*); -DPNTF_NO_LOOKAHEAD restores the plain poll
+#endif
 template <int S, class CTL>
 __device__ __forceinline__ void mma_block(CTL* ctl, uint32_t ring_addr, uint32_t opnd_addr, uint32_t d_tmem, int kh,
                                           bool accumulate_first, uint32_t& it) {
@@ -350,8 +353,26 @@ __device__ __forceinline__ void mma_block(CTL* ctl, uint32_t ring_addr, uint32_t
   constexpr uint32_t a_hi = desc_hi(1024), b_hi = desc_hi(kActSBO);
 #pragma unroll
   for (int s2 = 0; s2 < 2; ++s2) {
+#ifdef PNTF_LOOKAHEAD
+    // Bit 31 of `it`: this stage was already seen full by the look-ahead poll of the previous stage.  The poll of the
+    // NEXT stage's barrier is issued before this stage's UMMAs and its result is read after them, so its latency
+    // (100-250 clk for a ready barrier) is hidden behind the issue instead of preceding it.
+    const uint32_t n = it & 0x7fffffffu;
+    const uint32_t slot = n % S, ph = (n / S) & 1;
+    if (!(it >> 31)) mbar_spin(&ctl->full[slot], ph);
+    __syncwarp();
+    uint32_t ok_next;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok_next)
+        : "r"(smem_u32(&ctl->full[(n + 1) % S])), "r"(((n + 1) / S) & 1)
+        : "memory");
+#else
     const uint32_t slot = it % S, ph = (it / S) & 1;
     mbar_spin(&ctl->full[slot], ph);
+#endif
     tc_fence_after();
     if (elect_one()) {
       const uint32_t a_lo = desc_lo(ring_addr + slot * kStageBytes, 16);
@@ -363,7 +384,11 @@ __device__ __forceinline__ void mma_block(CTL* ctl, uint32_t ring_addr, uint32_t
       umma_commit(&ctl->empty[slot]);
     }
     __syncwarp();
+#ifdef PNTF_LOOKAHEAD
+    it = (n + 1) | (ok_next << 31);
+#else
     ++it;
+#endif
   }
 }
 
