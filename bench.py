@@ -336,7 +336,7 @@ def run_b200(args):
                 "hbm_peak_GBps": pk["hbm"],
                 "hbm_frac": (per_pair * n_total * args.steps / (top_ms * 1e-3) / 1e9 / pk["hbm"]) if per_pair else None,
                 "note": "the training kernels move 3.37 MB of activation stash per 128-row tile (12 pairs at d=3, 8 at d=6) through "
-                        "HBM; see DESIGN.md section 7 (forward 86 % of the 3.89 TB/s write-only peak, dW at the read peak; the MMA phases of forward and reverse are shared-memory-bandwidth bound: 12 KB of operand + weight-fill traffic per 128x128x16 UMMA)", "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
+                        "HBM; see DESIGN.md section 7 (forward 86 % of the 3.89 TB/s write-only peak, dW at the read peak)", "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
                 "launch_ms_avg": top_ms / max(top_cnt, 1), "launches": top_cnt,
                 "share_of_step": top_ms / max(step_ms_kernels, 1e-9),
                 "alg_flop_per_pair": class_flop[top_name],
