@@ -343,6 +343,19 @@ __device__ __forceinline__ void epi_publish_each(uint64_t* bar) {
 // warp 100-250 clk and the UMMA queue is shallow, so the per-stage poll + commit keeps the pipe at ~110-130 clk per
 // UMMA (floor 64).  A ring of three 32 KB blocks (one poll per 8 UMMAs, same smem look-ahead) was tried and was
 // 4 ms per 1 Mi pairs SLOWER in the training forward (coarser slot release), so the 16 KB stages stay.
+// Weight-ring slot release.  Default: one tcgen05.commit per 16 KB stage.  -DPNTF_PAIR_COMMIT (experiment): mma_block
+// consumes stages in pairs (2m, 2m+1) and commits once, after the second, on that stage's barrier; the producer, before
+// refilling the slot of stage n (last used by stage c = n - S), waits for the commit of the pair c belongs to.
+template <int S, class CTL>
+__device__ __forceinline__ void ring_wait_free(CTL* ctl, uint32_t n) {
+#ifdef PNTF_PAIR_COMMIT
+  if (n < uint32_t(S)) return;
+  const uint32_t c = (n - S) | 1u;   // the odd stage of the pair
+  mbar_wait(&ctl->empty[c % S], (c / (2 * S)) & 1);
+#else
+  mbar_wait(&ctl->empty[n % S], ((n / S) & 1) ^ 1);
+#endif
+}
 #ifndef PNTF_NO_LOOKAHEAD
 #define PNTF_LOOKAHEAD 1   // +4-5 % on the no-stash forward (profiles/r01m_*); -DPNTF_NO_LOOKAHEAD restores the plain poll
 #endif
@@ -381,7 +394,11 @@ __device__ __forceinline__ void mma_block(CTL* ctl, uint32_t ring_addr, uint32_t
       for (int j = 0; j < 4; ++j)
         umma_f16_split(d_tmem, a_lo + 2 * j, a_hi, b_lo + j * ((2 * kActSBO) >> 4), b_hi, idesc,
                        (accumulate_first || s2 > 0 || j > 0) ? 1u : 0u);
+#ifdef PNTF_PAIR_COMMIT
+      if (s2 == 1) umma_commit(&ctl->empty[slot]);
+#else
       umma_commit(&ctl->empty[slot]);
+#endif
     }
     __syncwarp();
 #ifdef PNTF_LOOKAHEAD
@@ -441,7 +458,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
         }
         for (int g = 0; g < kFwdStages; ++g) {
           const uint32_t slot = it % S, ph = (it / S) & 1;
-          mbar_wait(&ctl.empty[slot], ph ^ 1);
+          ring_wait_free<S>(&ctl, it);
           mbar_arrive_expect_tx(&ctl.full[slot], kStageBytes);
           bulk_g2s(ring + slot * kStageBytes, a.wimg + size_t(g) * kStageBytes, kStageBytes, &ctl.full[slot]);
           ++it;

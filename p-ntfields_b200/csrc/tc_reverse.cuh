@@ -278,7 +278,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         for (int g = 0; g < kRevStages; ++g) {
           const uint32_t slot = it % S, ph = (it / S) & 1;
-          mbar_wait(&ctl.empty[slot], ph ^ 1);
+          ring_wait_free<S>(&ctl, it);
           mbar_arrive_expect_tx(&ctl.full[slot], kStageBytes);
           bulk_g2s(ring + slot * kStageBytes, b.rimg + size_t(g) * kStageBytes, kStageBytes, &ctl.full[slot]);
           ++it;
