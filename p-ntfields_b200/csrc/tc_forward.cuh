@@ -314,6 +314,7 @@ struct TcCtl {
   // TC_TAIL_PLAN: the number of passes is data dependent; an epilogue thread announces every pass
   uint64_t go;                  // completes once per announcement
   volatile int more;            // 1 = another pass follows, 0 = the CTA is done
+  uint32_t ready;               // PNTF_HELPER_POLL: weight stages landed so far (written by the helper thread)
 };
 
 // all epilogue threads (converged warps): half h of the next operand tile (and its TMEM pre-loads) is complete.
@@ -359,14 +360,26 @@ __device__ __forceinline__ void ring_wait_free(CTL* ctl, uint32_t n) {
 #ifndef PNTF_NO_LOOKAHEAD
 #define PNTF_LOOKAHEAD 1   // +4-5 % on the no-stash forward (profiles/r01m_*); -DPNTF_NO_LOOKAHEAD restores the plain poll
 #endif
-template <int S, class CTL>
+template <int S, bool HELPER = false, class CTL>
 __device__ __forceinline__ void mma_block(CTL* ctl, uint32_t ring_addr, uint32_t opnd_addr, uint32_t d_tmem, int kh,
                                           bool accumulate_first, uint32_t& it) {
   constexpr uint32_t idesc = make_idesc(128, kRows, false, true);
   constexpr uint32_t a_hi = desc_hi(1024), b_hi = desc_hi(kActSBO);
 #pragma unroll
   for (int s2 = 0; s2 < 2; ++s2) {
-#ifdef PNTF_LOOKAHEAD
+#if defined(PNTF_HELPER_POLL)
+    // experiment: a helper thread observes the `full` barriers and publishes the number of landed stages in shared
+    // memory; the issuer reads that word (a shared-memory load instead of a barrier poll)
+    uint32_t slot;
+    if constexpr (HELPER) {
+      slot = it % S;
+      uint32_t spins = 0;
+      while (ld_acquire_u32(&ctl->ready) <= it) { if (++spins > (1u << 30)) __trap(); }
+    } else {
+      slot = it % S;
+      mbar_spin(&ctl->full[slot], (it / S) & 1);
+    }
+#elif defined(PNTF_LOOKAHEAD)
     // Bit 31 of `it`: this stage was already seen full by the look-ahead poll of the previous stage.  The poll of the
     // NEXT stage's barrier is issued before this stage's UMMAs and its result is read after them, so its latency
     // (100-250 clk for a ready barrier) is hidden behind the issue instead of preceding it.
@@ -401,7 +414,9 @@ __device__ __forceinline__ void mma_block(CTL* ctl, uint32_t ring_addr, uint32_t
 #endif
     }
     __syncwarp();
-#ifdef PNTF_LOOKAHEAD
+#if defined(PNTF_HELPER_POLL)
+    ++it;
+#elif defined(PNTF_LOOKAHEAD)
     it = (n + 1) | (ok_next << 31);
 #else
     ++it;
@@ -409,6 +424,13 @@ __device__ __forceinline__ void mma_block(CTL* ctl, uint32_t ring_addr, uint32_t
   }
 }
 
+// One thread issues a 16 KB bulk copy every ~230-260 clk (64-73 B/clk, scripts/l2_stream.cu, scripts/umma_smem_bw.cu):
+// exactly what the tensor pipe consumes at its peak, with no slack.  Two lanes of the producer warp, taking the
+// stages in turn, deliver ~100 B/clk without another warp (more warps made ptxas spill).
+#ifndef PNTF_PRODUCER_LANES
+#define PNTF_PRODUCER_LANES 1
+#endif
+constexpr int kProducerLanes = PNTF_PRODUCER_LANES;
 constexpr int kFwdRing = 5;                 // weight ring depth of the forward kernel
 
 template <int D, int ORDER, bool TRAIN, int TAIL>
@@ -437,6 +459,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     for (int i = 0; i < 4; ++i) mbar_init(&ctl.sd[i >> 1][i & 1], 1);
     for (int i = 0; i < 4; ++i) mbar_init(&ctl.xio[i >> 1][i & 1], 1);
     mbar_init(&ctl.go, 1);
+    ctl.ready = 0;
     fence_barrier_init();
   }
   if (warp == kMmaWarp) tmem_alloc(&ctl.tmem_base, 512);
@@ -448,7 +471,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
 
   if (warp == kProducerWarp) {
     // ------------------------------------------------------------- weight-stage producer
-    if (lane_id == 0) {
+    if (lane_id < kProducerLanes) {
       uint32_t it = 0, npass = 0;
       for (int64_t tile = blockIdx.x; PLAN || tile < ntiles; tile += gridDim.x) {
         if constexpr (PLAN) {
@@ -456,12 +479,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
           ++npass;
           if (!ctl.more) break;
         }
-        for (int g = 0; g < kFwdStages; ++g) {
-          const uint32_t slot = it % S, ph = (it / S) & 1;
+        for (int g = 0; g < kFwdStages; ++g, ++it) {
+          if (int(it % kProducerLanes) != lane_id) continue;   // the lanes take the stages in turn
+          const uint32_t slot = it % S;
           ring_wait_free<S>(&ctl, it);
           mbar_arrive_expect_tx(&ctl.full[slot], kStageBytes);
           bulk_g2s(ring + slot * kStageBytes, a.wimg + size_t(g) * kStageBytes, kStageBytes, &ctl.full[slot]);
-          ++it;
         }
       }
     }
@@ -501,7 +524,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
           trace_evt(a.trace, lane_id == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x, 0, l, kh);   // operand half kh seen
 #pragma unroll 1
           for (int h = 0; h < MH; ++h) {
-            mma_block<S>(&ctl, ring_addr, act_addr + (l & 1) * kTileBytes, acc + h * 128, kh, skip || kh > 0, it);
+            mma_block<S, !TRAIN>(&ctl, ring_addr, act_addr + (l & 1) * kTileBytes, acc + h * 128, kh, skip || kh > 0, it);
             if (kh == KH - 1) {
               if (elect_one()) umma_commit(&ctl.ar[h]);
               __syncwarp();
@@ -512,6 +535,26 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
       }
     }
   } else if (warp == kIoWarp) {
+#ifdef PNTF_HELPER_POLL
+    if constexpr (!TRAIN) {
+      // helper: follows the producer's stage sequence, observes each `full` barrier and publishes the stage count
+      if (lane_id == 0) {
+        uint32_t it = 0, npass = 0;
+        for (int64_t tile = blockIdx.x; PLAN || tile < ntiles; tile += gridDim.x) {
+          if constexpr (PLAN) {
+            mbar_wait(&ctl.go, npass & 1);
+            ++npass;
+            if (!ctl.more) break;
+          }
+          for (int g = 0; g < kFwdStages; ++g) {
+            mbar_spin(&ctl.full[it % S], (it / S) & 1);
+            ++it;
+            st_release_u32(&ctl.ready, it);
+          }
+        }
+      }
+    }
+#endif
     // ------------------------------------------------------------- training-stash stores
     if constexpr (TRAIN) {
       if (lane_id == 0) {

@@ -273,15 +273,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
   const int64_t ntiles = (a.pair_count + P - 1) / P;
 
   if (warp == kProducerWarp) {
-    if (lane_id == 0) {
+    if (lane_id < kProducerLanes) {
       uint32_t it = 0;
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        for (int g = 0; g < kRevStages; ++g) {
-          const uint32_t slot = it % S, ph = (it / S) & 1;
+        for (int g = 0; g < kRevStages; ++g, ++it) {
+          if (int(it % kProducerLanes) != lane_id) continue;   // the lanes take the stages in turn
+          const uint32_t slot = it % S;
           ring_wait_free<S>(&ctl, it);
           mbar_arrive_expect_tx(&ctl.full[slot], kStageBytes);
           bulk_g2s(ring + slot * kStageBytes, b.rimg + size_t(g) * kStageBytes, kStageBytes, &ctl.full[slot]);
-          ++it;
         }
       }
     }
