@@ -9,7 +9,7 @@
 using namespace pntf::tc;
 constexpr int S = 4;             // copies in flight per producer thread
 constexpr int kMaxProd = 4;
-__global__ void __launch_bounds__(768, 1) k(const uint8_t* img, long long* out, int numma, int n_rows, int producers, int writers, int commit_every) {
+__global__ void __launch_bounds__(768, 1) k(const uint8_t* img, long long* out, int numma, int n_rows, int producers, int writers, int commit_every, int tmem_readers = 0) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* act = smem;                       // 64 KB operand tile (B)
@@ -66,6 +66,20 @@ __global__ void __launch_bounds__(768, 1) k(const uint8_t* img, long long* out, 
       const long long t1 = clock64();
       if (lane == 0) out[blockIdx.x * 2 + 1] = n * producers * kStageBytes * 100 / (t1 - t0);
     }
+  } else if (warp >= 2 && warp < 2 + tmem_readers) {
+    // epilogue-like TMEM traffic: tcgen05.ld of 32 columns + tcgen05.st of 32 columns per iteration, in the half of
+    // TMEM the UMMAs do not touch (columns 256..511)
+    float v[32];
+    const uint32_t taddr = tb + (uint32_t((warp & 3) * 32) << 16) + 256 + 32 * ((warp >> 2) & 3);
+    float acc = 0.f;
+    while (!stop) {
+      tmem_ld<32>(taddr, v);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) { acc += v[i]; v[i] = acc; }
+      tmem_st<32>(taddr, v);
+      tmem_st_wait();
+    }
+    if (acc == 123.456f) out[0] = 1;
   } else if (warp >= 2 && warp < 2 + writers) {
     // st.shared streams: 16 B per thread per store, conflict-free
     uint4 v = make_uint4(t, t, t, t);
@@ -86,6 +100,15 @@ int main() {
   cudaMalloc(&img, 68 * 16384); cudaMemset(img, 0, 68 * 16384); cudaMalloc(&d, 148 * 16);
   const int smem = 65536 + 16384 + 4 * 16384 + 16384 + 1024;
   cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  for (int tmem_readers : {0, 4, 8, 16}) {
+    cudaMemset(d, 0, 148 * 16);
+    k<<<148, 64 + 32 * 16, smem>>>(img, d, 8000, 128, 1, 0, 4, tmem_readers);
+    cudaError_t e = cudaDeviceSynchronize();
+    std::vector<long long> h(296); cudaMemcpy(h.data(), d, 148 * 16, cudaMemcpyDeviceToHost);
+    double s = 0; for (int i = 0; i < 148; ++i) s += h[2 * i];
+    printf("N=128, commit every 4, 1 producer, %2d warps of tcgen05.ld+st (32 columns) beside it : %6.1f clk/UMMA (%s)\n",
+           tmem_readers, s / 148 / 100, cudaGetErrorString(e));
+  }
   for (int n_rows : {128})
     for (int commit_every : {0, 4, 8, 16})
       for (int producers : {0, 1}) {
