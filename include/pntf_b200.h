@@ -98,7 +98,8 @@ int pntf_loss_bwd(int variant, const float* params, const float* B, const float*
  * speed = batch[:, 2d:]; single: FastTensorDataLoader, models/model_res_sigmoid.py:30-73).
  * dataset[dataset_rows, 2d+2] is the GPU-resident table in the reference's layout (sampled_points ++ speed,
  * models/data_multi.py:15-31; several environments are stacked row-wise); pair p of the [E, N] batch is row
- * index[p] of it.  Nothing is materialised: coordinates and speeds are read through the index. */
+ * index[p] of it.  Nothing is materialised: coordinates and speeds are read through the index.  Every index value
+ * must lie in [0, dataset_rows): the kernels do not check it (the index lives on the device). */
 int pntf_loss_fwd_gather(int variant, const float* params, const float* B, const float* dataset, int64_t dataset_rows,
                          const int32_t* index, int E, int64_t N, int d, float alpha, float beta, float gamma,
                          float* diff, float* loss_out, int prec,
@@ -140,8 +141,10 @@ int pntf_mesh_distance(const float* triangles, int64_t M, const float* points, i
 /* Measurement aid for bench.py: between begin and end every kernel (group) the library launches is
  * bracketed by CUDA events on its stream; end synchronises on them and returns, per kernel class
  * (0 pack, 1 forward, 2 reverse, 3 dW, 4 loss-finalize, 5 adamw, 6 plan, 7 tc-forward, 8 tc-reverse,
- * 9 tc-dW), the summed device time in ms and the number of bracketed launches (groups). */
-#define PNTF_KERNEL_CLASSES 10
+ * 9 tc-dW, 10 tc-backward = reverse sweep + weight gradients in one launch), the summed device time in ms and the
+ * number of bracketed launches (groups).  Process-global, unsynchronised state: call from the one host thread that
+ * drives the library, for measurement only. */
+#define PNTF_KERNEL_CLASSES 11
 int pntf_profile_begin(void);
 int pntf_profile_end(double* ms_by_class, int64_t* count_by_class, int n_classes);
 

@@ -141,6 +141,10 @@ static int forward_dispatch(int order, int tail, const FwdArgs& a, cudaStream_t 
   return launch_forward<D, 2, false, TAIL_NONE>(a, s);
 }
 
+static int check_prec(int prec) {
+  if (prec != PNTF_PREC_FP32 && prec != PNTF_PREC_TC) return fail(PNTF_ERR_ARG, "bad precision mode %d", prec);
+  return PNTF_OK;
+}
 static int check_common(const void* params, const void* B, const void* coords, int E, int64_t N, int d) {
   if (!params || !B || (!coords && N > 0)) return fail(PNTF_ERR_ARG, "null pointer argument");
   if (E < 1 || N < 0) return fail(PNTF_ERR_ARG, "bad shape E=%d N=%lld", E, (long long)N);
@@ -294,10 +298,13 @@ int pntf_forward(int mode, int grad_flavour, const float* params, const float* B
                  int d, float* tau, float* dtau, float* ltau, int prec, void* workspace, size_t workspace_bytes,
                  void* stream) {
   if (mode < 0 || mode > 2) return fail(PNTF_ERR_ARG, "bad mode %d", mode);
+  if (int rc = check_prec(prec)) return rc;
   if (grad_flavour == PNTF_GRAD_COMPAT && mode != PNTF_MODE_GRAD)
     return fail(PNTF_ERR_ARG, "the compat gradient flavour exists for MODE_GRAD only");
-  if (prec == PNTF_PREC_TC)
+  if (prec == PNTF_PREC_TC) {
+    if (int rc = check_common(params, B, coords, E, N, d)) return rc;
     return tc_forward(mode, grad_flavour, params, B, coords, E, N, d, tau, dtau, ltau, workspace, workspace_bytes, stream);
+  }
   return forward_common(mode, TAIL_NONE, 0, grad_flavour, params, B, coords, nullptr, E, N, d, 1.f, 0.f, 0, tau, dtau,
                         ltau, nullptr, nullptr, workspace, workspace_bytes, stream);
 }
@@ -305,6 +312,7 @@ int pntf_forward(int mode, int grad_flavour, const float* params, const float* B
 int pntf_field(int kind, int grad_flavour, const float* params, const float* B, const float* coords, int E, int64_t N,
                int d, float gamma, float* out, int prec, void* workspace, size_t workspace_bytes, void* stream) {
   if (kind < 0 || kind > 3 || !out) return fail(PNTF_ERR_ARG, "bad field kind %d or null output", kind);
+  if (int rc = check_prec(prec)) return rc;
   if (grad_flavour == PNTF_GRAD_COMPAT && kind != PNTF_FIELD_DIRECTION)
     return fail(PNTF_ERR_ARG, "the compat gradient flavour exists for FIELD_DIRECTION only");
   const int order = (kind == PNTF_FIELD_TRAVEL_TIME) ? 0 : (kind == PNTF_FIELD_SPEED2 ? 2 : 1);
@@ -333,6 +341,8 @@ int pntf_loss_fwd(int variant, const float* params, const float* B, const float*
                   void* workspace, size_t workspace_bytes, void* stream) {
   if (variant != PNTF_LOSS_SINGLE && variant != PNTF_LOSS_MULTI) return fail(PNTF_ERR_ARG, "bad loss variant");
   if (!speed || !diff || !loss_out) return fail(PNTF_ERR_ARG, "null speed/diff/loss_out");
+  if (int rc = check_prec(prec)) return rc;
+  if (int rc = check_common(params, B, coords, E, N, d)) return rc;
   if (N == 0) return fail(PNTF_ERR_ARG, "empty batch has no loss");
   if (prec == PNTF_PREC_TC)
     return tc_loss(0, variant, params, B, coords, speed, E, N, d, alpha, beta, gamma, diff, loss_out, nullptr,
@@ -349,6 +359,7 @@ int pntf_loss_bwd(int variant, const float* params, const float* B, const float*
                   float* grad_params, int prec, void* workspace, size_t workspace_bytes, void* stream) {
   if (variant != PNTF_LOSS_SINGLE && variant != PNTF_LOSS_MULTI) return fail(PNTF_ERR_ARG, "bad loss variant");
   if (!speed || !diff || !loss_out || !grad_params) return fail(PNTF_ERR_ARG, "null speed/diff/loss_out/grad_params");
+  if (int rc = check_prec(prec)) return rc;
   if (int rc = check_common(params, B, coords, E, N, d)) return rc;
   if (N == 0) return fail(PNTF_ERR_ARG, "empty batch has no loss");
   if (prec == PNTF_PREC_TC)
@@ -423,6 +434,7 @@ int pntf_plan(const float* params, const float* B, const float* start_goal, int6
               size_t workspace_bytes, void* stream) {
   if (int rc = check_common(params, B, start_goal, 1, Q, d)) return rc;
   if (!waypoints || !nsteps || max_iter < 0) return fail(PNTF_ERR_ARG, "bad plan argument");
+  if (int rc = check_prec(prec)) return rc;
   if (Q == 0) return PNTF_OK;
   if (prec == PNTF_PREC_TC)
     return tc_plan(params, B, start_goal, Q, d, eta, thr, max_iter, grad_flavour, waypoints, nsteps, workspace,

@@ -9,7 +9,7 @@ namespace pntf {
 
 // helpers defined in capi.cu
 enum { KC_PACK = 0, KC_FORWARD, KC_REVERSE, KC_DW, KC_FINALIZE, KC_ADAMW, KC_PLAN, KC_TC_FORWARD, KC_TC_REVERSE,
-       KC_TC_DW, KC_COUNT };
+       KC_TC_DW, KC_TC_BACKWARD, KC_COUNT };
 int fail(int code, const char* fmt, ...);
 void prof_start(int cls, cudaStream_t s);
 void prof_stop(cudaStream_t s);

@@ -23,7 +23,22 @@ struct TcDwArgs {
   int64_t ntiles;
   float* grad;
   float out_scale;
+  // fused backward (tc_backward.cuh): wait for flags[tile * 16 + l] == epoch before reading Ybar_l of a tile
+  const uint32_t* flags;
+  uint32_t epoch;
 };
+
+// acquire side of the reverse sweep's flags (tc_reverse.cuh: flag_publish)
+__device__ __forceinline__ void dw_flag_wait(const uint32_t* flag, uint32_t epoch) {
+  uint32_t v, spins = 0;
+  for (;;) {
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+    if (v == epoch) break;
+    __nanosleep(64);
+    if (++spins > (1u << 25)) __trap();   // seconds: a protocol bug traps instead of hanging the GPU
+  }
+  asm volatile("fence.proxy.async;" ::: "memory");
+}
 
 constexpr int kDwStageBytes = 128 * 256 + 256 * 256;   // Ybar half tile + X tile
 constexpr int kDwStages = 2;
@@ -34,16 +49,18 @@ struct TcDwCtl {
   uint32_t tmem_base;
 };
 
-__global__ void __launch_bounds__(kDwThreads, 1) tc_dw_kernel(const TcDwArgs a) {
+// `cta`: index of this CTA among the weight-gradient CTAs of the launch.  Warps 0..7 drain, warp 8 loads, warp 9 issues;
+// further warps of the block (fused launch: the block has the reverse sweep's size) only take part in the barriers.
+__device__ __forceinline__ void tc_dw_role(const TcDwArgs& a, const int cta) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ TcDwCtl ctl;
   const int tid = threadIdx.x, warp = tid >> 5, lane_id = tid & 31;
   int u = 0;
   for (int i = 1; i < a.units.n; ++i)
-    if (int(blockIdx.x) >= a.units.cta_begin[i]) u = i;
+    if (cta >= a.units.cta_begin[i]) u = i;
   const int l = a.units.l[u], h = a.units.h[u];
-  const int rank = int(blockIdx.x) - a.units.cta_begin[u];
+  const int rank = cta - a.units.cta_begin[u];
   const int ncta = a.units.cta_begin[u + 1] - a.units.cta_begin[u];
   const int K = c_K[l], M = c_M[l];
   const int64_t my_tiles = (a.ntiles > rank) ? (a.ntiles - rank + ncta - 1) / ncta : 0;
@@ -66,6 +83,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) tc_dw_kernel(const TcDwArgs a) 
         const int64_t tile = rank + i * ncta;
         const uint32_t slot = uint32_t(i % kDwStages), ph = uint32_t(i / kDwStages) & 1;
         mbar_wait(&ctl.empty[slot], ph ^ 1);
+        if (a.flags != nullptr) dw_flag_wait(a.flags + size_t(tile) * 16 + l, a.epoch);
         mbar_arrive_expect_tx(&ctl.full[slot], 128 * 256 + xbytes);
         uint8_t* dst = smem + slot * kDwStageBytes;
         bulk_g2s(dst, a.st.G[l] + (size_t(tile) * M + size_t(h) * 128) * 256, 128 * 256, &ctl.full[slot]);
@@ -90,7 +108,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) tc_dw_kernel(const TcDwArgs a) 
       }
       umma_commit(&ctl.done);
     }
-  } else if (my_tiles > 0) {
+  } else if (warp < 8 && my_tiles > 0) {
     mbar_wait(&ctl.done, 0);
     tc_fence_after();
     const int m = tid & 127, half = tid >> 7;
@@ -111,6 +129,9 @@ __global__ void __launch_bounds__(kDwThreads, 1) tc_dw_kernel(const TcDwArgs a) 
   __syncthreads();
   if (warp == 9) tmem_dealloc(tmem_base, 256);
 }
+
+// stand-alone launch (PNTF_BWD_SPLIT=1), after the reverse kernel has finished
+__global__ void __launch_bounds__(kDwThreads, 1) tc_dw_kernel(const TcDwArgs a) { tc_dw_role(a, int(blockIdx.x)); }
 
 }  // namespace tc
 }  // namespace pntf

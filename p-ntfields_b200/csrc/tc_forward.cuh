@@ -731,8 +731,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
       TcTile<C>& t0 = ts[0];
       if (tid < P) active[tid] = 0;
       if (tid == 0) { ndone[0] = 0; ndone[1] = 0; }
-#pragma unroll 1
       bool drained = false;   // the query counter ran past the end: this slot stays empty
+#pragma unroll 1
       for (uint32_t round = 0;; ++round) {
         if (tid < P && !active[tid] && !drained) {
           // refill this slot

@@ -6,9 +6,7 @@
 
 #include "../../include/pntf_b200.h"
 #include "tc_api.cuh"
-#include "tc_dw.cuh"
-#include "tc_forward.cuh"
-#include "tc_reverse.cuh"
+#include "tc_backward.cuh"
 
 namespace pntf {
 
@@ -89,7 +87,7 @@ static size_t stash_tile_bytes() {
   size_t s = 0;
   for (int l = 0; l <= 13; ++l) s += size_t(layer_desc(l).K) * 256;
   for (int l = 0; l <= 12; ++l) s += size_t(layer_desc(l).M) * 256;
-  return s + kHalfTileBytes + kRows * sizeof(float);
+  return s + kHalfTileBytes + kRows * sizeof(float) + kFlagStride * sizeof(uint32_t);
 }
 // Column mode of the loss kernels: summed Laplacian columns (TcCfg: kOrderLapSum, default) or one second-order column
 // per coordinate (PNTF_LOSS_COLUMNS=full; same results, kept as a cross-check).
@@ -125,6 +123,8 @@ static void tc_carve_stash(TcStash& st, uint8_t* base, size_t tiles) {
   st.Y5 = base + off; off += tiles * kHalfTileBytes;
   st.y13 = reinterpret_cast<float*>(base + off);
 }
+// per-(tile, layer) flags of the fused backward launch: behind the y13 rows
+static uint32_t* stash_flags(const TcStash& st, size_t tiles) { return reinterpret_cast<uint32_t*>(st.y13 + tiles * kRows); }
 
 // work units of the weight-gradient kernel: (layer, 128-feature half), CTAs proportional to the bytes a
 // unit streams per tile (32 KB of Ybar + K*256 B of X)
@@ -144,6 +144,49 @@ static DwUnits make_dw_units(int sms) {
   return u;
 }
 
+// Fused backward: `ncta` weight-gradient CTAs over the 19 (layer, half) units in proportion to the tensor time a unit
+// needs per tile (K = 256: eight N = 256 UMMAs, K = 128: eight N = 128 UMMAs), at least one each.
+static DwUnits make_dw_units_for(int ncta) {
+  DwUnits u{};
+  int n = 0;
+  int cost[kDwMaxUnits], cnt[kDwMaxUnits];
+  for (int l = 0; l <= 12; ++l)
+    for (int h = 0; h < (layer_desc(l).M + 127) / 128; ++h) {
+      u.l[n] = l; u.h[n] = h;
+      cost[n] = layer_desc(l).K == 256 ? 2 : 1;
+      cnt[n] = 1;
+      ++n;
+    }
+  u.n = n;
+  for (int extra = ncta - n; extra > 0; --extra) {
+    int best = 0;
+    for (int i = 1; i < n; ++i)
+      if (cost[i] * cnt[best] > cost[best] * cnt[i]) best = i;   // largest cost per CTA
+    ++cnt[best];
+  }
+  int cta = 0;
+  for (int i = 0; i < n; ++i) { u.cta_begin[i] = cta; cta += cnt[i]; }
+  u.cta_begin[n] = cta;
+  return u;
+}
+// CTAs of the fused backward launch given to the weight-gradient role (0: separate launches, the default).
+// PNTF_DW_CTAS=n turns the fused launch on with n weight-gradient CTAs.  Measured (profiles/r02a_*): correct (same parity
+// tests) but slower than separate launches -- 66.9 ms against 30.0 + 16.8 ms per 1 Mi pairs with n = 48: a weight-gradient
+// CTA holds only two 96 KB stages, runs latency-bound at ~2 900 clk per tile, falls behind the sweep and then reads from
+// HBM after all.
+static int fused_dw_ctas(int64_t tiles) {
+  static const int forced = [] {
+    const char* e = getenv("PNTF_DW_CTAS");
+    return e != nullptr ? atoi(e) : 0;
+  }();
+  const int sms = sm_count();
+  int n = forced;
+  if (n <= 0) return 0;
+  if (n < kDwMaxUnits) n = kDwMaxUnits;
+  if (sms - n < 8 || tiles < 1) return 0;
+  return n;
+}
+
 template <int D, int ORDER>
 static int tc_loss_bwd(int variant, const float* params, const float* B, const float* coords, const float* speed, int E,
                        int64_t N, float alpha, float beta, float gamma, float* diff, float* grad_params, uint8_t* ws,
@@ -160,12 +203,17 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
   if (int rc = tc_pack(params, fimg, rimg, s)) return rc;
   auto kf = tc_forward_kernel<D, ORDER, true, TC_TAIL_LOSS>;
   auto kr = tc_reverse_kernel<D, ORDER>;
+  auto kb = tc_backward_kernel<D, ORDER>;
   const size_t smem_f = kFwdSmem, smem_r = kRevSmem;
   const size_t smem_d = size_t(kDwStages) * kDwStageBytes + 1024;
   if (int rc = tc_set_smem(kf, smem_f)) return rc;
   if (int rc = tc_set_smem(kr, smem_r)) return rc;
   if (int rc = tc_set_smem(tc_dw_kernel, smem_d)) return rc;
-  const DwUnits units = make_dw_units(sm_count());
+  static_assert(kRevSmem >= size_t(kDwStages) * kDwStageBytes + 1024, "the fused launch uses the reverse sweep's shared memory size");
+  if (int rc = tc_set_smem(kb, smem_r)) return rc;
+  const int n_dw = fused_dw_ctas(chunk_tiles);
+  const DwUnits units = n_dw > 0 ? make_dw_units_for(n_dw) : make_dw_units(sm_count());
+  static uint32_t epoch = 0;
   const float out_scale = float(double(beta) / (double(E) * double(N)) / double(kGradScale));
   for (int64_t t0 = 0; t0 < ntiles_all; t0 += chunk_tiles) {
     const int64_t tiles = (ntiles_all - t0 < chunk_tiles) ? (ntiles_all - t0) : chunk_tiles;
@@ -187,6 +235,25 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     trace_end(a.trace, s, "tc_forward(train)");
     a.trace = nullptr;
     if (int rc = launch_check("tc_forward(train)")) return rc;
+    TcDwArgs dw{};
+    dw.st = a.st; dw.units = units; dw.ntiles = tiles; dw.grad = grad_params; dw.out_scale = out_scale;
+    if (n_dw > 0) {
+      // one launch: reverse sweep on the first CTAs, weight gradients trailing it on the last n_dw (tc_backward.cuh)
+      uint32_t* flags = stash_flags(a.st, size_t(tiles));
+      cudaError_t e = cudaMemsetAsync(flags, 0, size_t(tiles) * kFlagStride * sizeof(uint32_t), s);
+      if (e != cudaSuccess) return fail(PNTF_ERR_CUDA, "cudaMemsetAsync(flags): %s", cudaGetErrorString(e));
+      r.flags = flags; dw.flags = flags;
+      r.epoch = dw.epoch = ++epoch == 0 ? ++epoch : epoch;
+      const int n_rev = int(tiles < sm_count() - n_dw ? tiles : sm_count() - n_dw);
+      a.trace = (t0 == 0) ? trace_begin() : nullptr;
+      prof_start(KC_TC_BACKWARD, s);
+      kb<<<n_rev + n_dw, kTcThreads, smem_r, s>>>(r, dw, n_rev);
+      prof_stop(s);
+      trace_end(a.trace, s, "tc_backward (role 1: acc half 0 ready, stash inputs ready, half 0 published, half 1 published)");
+      a.trace = nullptr;
+      if (int rc = launch_check("tc_backward")) return rc;
+      continue;
+    }
     a.trace = (t0 == 0) ? trace_begin() : nullptr;
     prof_start(KC_TC_REVERSE, s);
     kr<<<grid, kTcThreads, smem_r, s>>>(r);
@@ -194,8 +261,6 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     trace_end(a.trace, s, "tc_reverse (role 1: acc half 0 ready, stash inputs ready, half 0 published, half 1 published)");
     a.trace = nullptr;
     if (int rc = launch_check("tc_reverse")) return rc;
-    TcDwArgs dw{};
-    dw.st = a.st; dw.units = units; dw.ntiles = tiles; dw.grad = grad_params; dw.out_scale = out_scale;
     prof_start(KC_TC_DW, s);
     tc_dw_kernel<<<units.cta_begin[units.n], kDwThreads, smem_d, s>>>(dw);
     prof_stop(s);

@@ -27,7 +27,20 @@ struct TcRevArgs {
   const uint8_t* rimg;      // reverse (transposed) stage images
   float* grad;              // flat parameter gradient (accumulated with atomics)
   float out_scale;          // beta / (E*N) / kGradScale
+  // Fused backward (tc_backward_kernel): flags[tile * kFlagStride + l] = epoch once Ybar_l of that tile is complete in
+  // global memory; the weight-gradient CTAs of the same launch wait on it.  nullptr: separate launches, no flags.
+  uint32_t* flags;
+  uint32_t epoch;
 };
+
+constexpr int kFlagStride = 16;   // flag words per tile (13 layers used)
+
+// cross-CTA hand-over of bulk-stored data: the writer has waited for its bulk groups (cp.async.bulk.wait_group), the
+// reader issues bulk loads after the acquire; the proxy fences order the async-proxy accesses against the flag
+__device__ __forceinline__ void flag_publish(uint32_t* flag, uint32_t epoch) {
+  asm volatile("fence.proxy.async;" ::: "memory");
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flag), "r"(epoch) : "memory");
+}
 
 // accumulator region of product l (1 = B) and the region the epilogue of step l reads
 static __constant__ int c_rev_acc[kNumLayers] = {0, 1, 0, 1, 0, 0, 1, 0, 1, 0, 1, 0, 1, 0};
@@ -236,7 +249,7 @@ constexpr int kNumBiasSlots = 2432;   // sum of M_l over l = 0..12: offsets c_db
 static __constant__ int c_db[kNumLayers] = {0, 128, 256, 384, 512, 640, 768, 1024, 1280, 1536, 1792, 2048, 2304, 2432};
 
 template <int D, int ORDER>
-__global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevArgs b) {
+__device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int cta, const int ncta) {
   using C = TcCfg<D, ORDER>;
   static_assert(ORDER == 2 || ORDER == kOrderLapSum, "the loss needs second-order columns");
   constexpr int S = kRevRing;
@@ -275,7 +288,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
   if (warp == kProducerWarp) {
     if (lane_id < kProducerLanes) {
       uint32_t it = 0;
-      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      for (int64_t tile = cta; tile < ntiles; tile += ncta) {
         for (int g = 0; g < kRevStages; ++g, ++it) {
           if (int(it % kProducerLanes) != lane_id) continue;   // the lanes take the stages in turn
           const uint32_t slot = it % S;
@@ -289,7 +302,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
     // converged warp, elected lane issues
     uint32_t it = 0, nx0 = 0, nx1 = 0;
     const uint32_t ring_addr = smem_u32(ring), gt_addr = smem_u32(gt);
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (int64_t tile = cta; tile < ntiles; tile += ncta) {
 #pragma unroll 1
       for (int l = 12; l >= 1; --l) {
         const int MH = halves(c_M[l]), OH = c_K[l] >> 7;
@@ -300,11 +313,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
           if (kh == 0) { mbar_spin(&ctl.xr[0], nx0 & 1); ++nx0; }
           else { mbar_spin(&ctl.xr[1], nx1 & 1); ++nx1; }
           tc_fence_after();
-          trace_evt(a.trace, lane_id == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x, 0, l, kh);
+          trace_evt(a.trace, lane_id == 0 && cta == 0 && tile == int64_t(cta) + 2 * ncta, 0, l, kh);
 #pragma unroll 1
           for (int h = 0; h < OH; ++h) {
             mma_block<S>(&ctl, ring_addr, gt_addr, acc + h * 128, kh, skip || kh > 0, it);
-            if (kh == MH - 1) trace_evt(a.trace, lane_id == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x, 0, l, 2 + h);
+            if (kh == MH - 1) trace_evt(a.trace, lane_id == 0 && cta == 0 && tile == int64_t(cta) + 2 * ncta, 0, l, 2 + h);
             if (kh == MH - 1) {
               if (elect_one()) {
                 if (MH == 1 && OH == 2) {
@@ -342,10 +355,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
         mbar_arrive_expect_tx(&ctl.yb[bh], kHalfTileBytes);
         bulk_g2s(xbuf + bh * kHalfTileBytes, src(l, tile) + size_t(sh) * kHalfTileBytes, kHalfTileBytes, &ctl.yb[bh]);
       };
-      load(12, blockIdx.x, 0, 0);
-      load(11, blockIdx.x, 1, 1);
-      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int64_t tn = tile + gridDim.x;
+      // fused backward: flag (tile, l) is published once the bulk group holding the last half of Ybar_l has completed;
+      // the check lags two groups behind the newest one, so it never waits for a store that was just issued
+      uint32_t ngrp = 0, pend_g[4] = {0, 0, 0, 0}, pend_i[4] = {0, 0, 0, 0}, ph = 0, pt = 0;
+      auto flush_flags = [&](uint32_t done_upto) {
+        while (ph != pt && pend_g[ph & 3] <= done_upto) {
+          flag_publish(b.flags + pend_i[ph & 3], b.epoch);
+          ++ph;
+        }
+      };
+      load(12, cta, 0, 0);
+      load(11, cta, 1, 1);
+      for (int64_t tile = cta; tile < ntiles; tile += ncta) {
+        const int64_t tn = tile + ncta;
 #pragma unroll 1
         for (int l = 12; l >= 0; --l) {
           const int M = c_M[l], MH = halves(M);
@@ -365,10 +387,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
             bulk_commit();
             bulk_wait_read<0>();
             mbar_arrive(&ctl.sd[kh]);    // the next epilogue may overwrite this half of the operand tile
+            if (b.flags != nullptr) {
+              ++ngrp;
+              if (kh == MH - 1) {
+                pend_g[pt & 3] = ngrp;
+                pend_i[pt & 3] = uint32_t(tile) * kFlagStride + uint32_t(l);
+                ++pt;
+              }
+              if (ngrp > 2) {
+                bulk_wait<2>();
+                flush_flags(ngrp - 2);
+              }
+            }
           }
         }
       }
       bulk_wait0();
+      if (b.flags != nullptr) flush_flags(ngrp);
     }
   } else {
     const EpiPos p = epi_pos(tmem_base);
@@ -377,10 +412,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
     const float w13f = __ldg(prm + c_w[13] + p.lane);
     float dw13 = 0.f, unused = 0.f;
     uint32_t nar0 = 0, nar1 = 0, ny0 = 0, ny1 = 0, nsd0 = 0, nsd1 = 0;
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (int64_t tile = cta; tile < ntiles; tile += ncta) {
       const int64_t pair0 = a.pair_begin + tile * P;
       int tl = 12;
-      const bool tron = tid == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x;
+      const bool tron = tid == 0 && cta == 0 && tile == int64_t(cta) + 2 * ncta;
       // ---- loss seeds and output-activation adjoint (one thread per pair), S:890-936 / M:914-951
       if (tid < P) {
         const int64_t pair = pair0 + tid;
@@ -455,10 +490,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
 #define PNTF_WAIT0_Y1() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); --tl; trace_evt(a.trace, tron, 1, tl, 0); PNTF_WAIT_SD0(); mbar_wait(&ctl.yb[1], ny1 & 1); ++ny1; trace_evt(a.trace, tron, 1, tl, 1); }
 #define PNTF_WAIT0() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); --tl; trace_evt(a.trace, tron, 1, tl, 0); PNTF_WAIT_SD0(); mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; trace_evt(a.trace, tron, 1, tl, 1); }
       // (operand-tile half 1 was last stored by step l+1, or for l = 11 by step 6 of the previous tile)
-#define PNTF_WAIT1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); if (l != 11 || tile != int64_t(blockIdx.x)) PNTF_WAIT_SD1(); mbar_wait(&ctl.yb[1], ny1 & 1); ++ny1; }
+#define PNTF_WAIT1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); if (l != 11 || tile != int64_t(cta)) PNTF_WAIT_SD1(); mbar_wait(&ctl.yb[1], ny1 & 1); ++ny1; }
 #define PNTF_DB(l, h, v) red_shared_add(sdb_addr + 4u * uint32_t(c_db[l] + (h) * 128 + p.lane), (v))
       // ---- generator (step 12 has no accumulator input; the operand tile was last stored by step 0 of the previous tile)
-      if (tile != int64_t(blockIdx.x)) PNTF_WAIT_SD0();
+      if (tile != int64_t(cta)) PNTF_WAIT_SD0();
       { mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; trace_evt(a.trace, tron, 1, 12, 1); }
       PNTF_DB(12, 0, (epi_adjoint_half<C, false, false, true>(p, 0, 0, p.lane, x_addr, gt_addr, g13s, w13f, dw13)));
       { epi_publish_each(&ctl.xr[0]); trace_evt(a.trace, tron, 1, tl, 2); }
@@ -525,6 +560,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevAr
   tc_fence_before();
   __syncthreads();
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
+}
+
+// stand-alone launch of the reverse sweep (PNTF_BWD_SPLIT=1: weight gradients by a separate tc_dw_kernel launch)
+template <int D, int ORDER>
+__global__ void __launch_bounds__(kTcThreads, 1) tc_reverse_kernel(const TcRevArgs b) {
+  tc_reverse_role<D, ORDER>(b, int(blockIdx.x), int(gridDim.x));
 }
 
 }  // namespace tc

@@ -108,7 +108,7 @@ def launch_count():
     return int(lib().pntf_launch_count())
 
 
-KERNEL_CLASSES = ("pack", "forward", "reverse", "dw", "finalize", "adamw", "plan", "tc_forward", "tc_reverse", "tc_dw")
+KERNEL_CLASSES = ("pack", "forward", "reverse", "dw", "finalize", "adamw", "plan", "tc_forward", "tc_reverse", "tc_dw", "tc_backward")
 
 
 def profile_begin():

@@ -1,7 +1,7 @@
 """Dataset readers compatible with the reference's on-disk layout.
 
 models/data_mlp.py:25-43   : DataPath/sampled_points.npy [Ns,2d], speed.npy [Ns,2]  -> one [Ns,2d+2] tensor
-models/data_multi.py:7-33  : DataPath/<env>/sampled_points.npy (rounded through fp16, :19), speed.npy, B.npy [d,128]
+models/data_multi.py:7-33  : DataPath + str(i) + /sampled_points.npy (rounded through fp16, :19), speed.npy, B.npy [d,128]
 """
 import os
 
@@ -16,10 +16,11 @@ def load_single(path):
 
 
 def load_multi(path, length):
-    envs = sorted(d for d in os.listdir(path) if os.path.isdir(os.path.join(path, d)))[:length]
+    """Environment i lives in ``path + str(i)`` for i in range(length), by plain string concatenation as in
+    models/data_multi.py:17 (so ``path`` is normally ``.../`` or a prefix such as ``.../env``)."""
     out = []
-    for e in envs:
-        p = os.path.join(path, e)
+    for i in range(int(length)):
+        p = path + str(i)
         pts = np.load(os.path.join(p, "sampled_points.npy")).astype(np.float16).astype(np.float32)
         spd = np.load(os.path.join(p, "speed.npy")).astype(np.float32)
         B = np.load(os.path.join(p, "B.npy")).astype(np.float32)

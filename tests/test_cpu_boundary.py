@@ -61,6 +61,26 @@ def test_argument_errors_without_gpu():
     assert rc == 1
     rc = L.pntf_loss_fwd(3, dummy, dummy, dummy, dummy, 1, 8, 3, 1.0, 1.0, 1e-3, dummy, dummy, 0, dummy, 1 << 30, None)
     assert rc == 1
+    # the tensor-core mode validates before dispatching as well (d outside {3, 6}, null pointers, E < 1, bad prec)
+    TC = capi.PREC_TC
+    rc = L.pntf_forward(capi.MODE_GRAD, 0, dummy, dummy, dummy, 1, 8, 4, dummy, dummy, dummy, TC, dummy, 1 << 30, None)
+    assert rc == 2 and b"d=4" in L.pntf_last_error()
+    rc = L.pntf_forward(capi.MODE_GRAD, 0, dummy, None, dummy, 1, 8, 3, dummy, dummy, dummy, TC, dummy, 1 << 30, None)
+    assert rc == 1
+    rc = L.pntf_forward(capi.MODE_GRAD, 0, dummy, dummy, dummy, 0, 8, 3, dummy, dummy, dummy, TC, dummy, 1 << 30, None)
+    assert rc == 1
+    rc = L.pntf_loss_fwd(1, dummy, dummy, dummy, dummy, 1, 8, 5, 1.0, 1.0, 1e-3, dummy, dummy, TC, dummy, 1 << 30, None)
+    assert rc == 2
+    rc = L.pntf_loss_fwd(1, None, dummy, dummy, dummy, 1, 8, 3, 1.0, 1.0, 1e-3, dummy, dummy, TC, dummy, 1 << 30, None)
+    assert rc == 1
+    rc = L.pntf_loss_bwd(1, dummy, dummy, dummy, dummy, 1, 8, 7, 1.0, 1.0, 1e-3, dummy, dummy, dummy, TC, dummy, 1 << 30, None)
+    assert rc == 2
+    rc = L.pntf_field(capi.FIELD_SPEED, 0, dummy, dummy, dummy, 1, 8, 2, 0.0, dummy, TC, dummy, 1 << 30, None)
+    assert rc == 2
+    rc = L.pntf_plan(dummy, dummy, dummy, 8, 9, 0.03, 0.06, 10, 0, dummy, dummy, TC, dummy, 1 << 30, None)
+    assert rc == 2
+    rc = L.pntf_forward(capi.MODE_GRAD, 0, dummy, dummy, dummy, 1, 8, 3, dummy, dummy, dummy, 5, dummy, 1 << 30, None)
+    assert rc == 1 and b"precision" in L.pntf_last_error()
     assert capi.lib().pntf_workspace_bytes(capi.OP_FORWARD, 1, 100, 4, 0, 0) == 0
     with pytest.raises(RuntimeError):
         capi.forward(capi.MODE_VALUE, torch.zeros(capi.PARAM_COUNT), torch.zeros(3, 128), torch.zeros(4, 6), 1, 4, 3)
