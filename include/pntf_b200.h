@@ -127,6 +127,14 @@ int pntf_plan(const float* params, const float* B, const float* start_goal, int6
               float* waypoints, int32_t* nsteps, int prec,
               void* workspace, size_t workspace_bytes, void* stream);
 
+/* Same integration; rows of waypoints after a query's last step (row nsteps[q]) are NOT written (the caller's buffer
+ * keeps whatever it held).  pntf_plan fills them with the final position, which at the reference's cap of 500 is
+ * 30x the bytes of the waypoints themselves; batched callers read waypoints[q, :nsteps[q]+1] only. */
+int pntf_plan_compact(const float* params, const float* B, const float* start_goal, int64_t Q, int d,
+                      float eta, float thr, int max_iter, int grad_flavour,
+                      float* waypoints, int32_t* nsteps, int prec,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
 /* Ground-truth speed sampling: unsigned distance from N query points [N,3] to a triangle soup
  * triangles[M,3,3] and, when speed != NULL, speed = clip(distance, offset, margin) / margin.
  * Replaces dataprocessing/speed_sampling_gpu.py:325-336 (point_obstacle_distance: sqrt of the squared distance of the
@@ -152,6 +160,14 @@ int pntf_profile_end(double* ms_by_class, int64_t* count_by_class, int n_classes
  * counterpart.  W, X, C: [128,128] fp32 device arrays; out[3,128,128] = {W X, C + W X, X X^T} computed
  * with fp16 operands and fp32 accumulation on the tensor cores. */
 int pntf_tc_selftest(const float* W, const float* X, const float* C, float* out, void* stream);
+
+/* Test aid for the tensor-core backward (no reference counterpart): statistics of the fp16 adjoint tiles the last
+ * pntf_loss_bwd(prec = PNTF_PREC_TC) call left in `workspace` (same E, N, d; the call must have fitted one chunk).
+ * Adjoints travel as scaled fp16; layer = -1: all adjoint tiles Ybar_0..12, 0..12: Ybar_layer, 100 + l: the forward
+ * operand tile X_l (l = 0..13).  out[4] (device, uint64) = {inf/NaN count, subnormal count, nonzero count, fp32 bit
+ * pattern of the largest finite magnitude}. */
+int pntf_debug_adjoint_stats(const void* workspace, size_t workspace_bytes, int E, int64_t N, int d, int layer,
+                             uint64_t* out, void* stream);
 
 /* number of kernels the library has launched since load (for bench.py's gpu_launches) */
 int64_t pntf_launch_count(void);

@@ -410,6 +410,12 @@ int pntf_loss_bwd_gather(int variant, const float* params, const float* B, const
                        grad_params, prec, workspace, workspace_bytes, stream);
 }
 
+int pntf_debug_adjoint_stats(const void* workspace, size_t workspace_bytes, int E, int64_t N, int d, int layer,
+                             uint64_t* out, void* stream) {
+  if (!workspace || !out || E < 1 || N < 1 || (d != 3 && d != 6)) return fail(PNTF_ERR_ARG, "bad adjoint-statistics argument");
+  return tc_debug_adjoint_stats(workspace, workspace_bytes, E, N, d, layer, reinterpret_cast<unsigned long long*>(out), stream);
+}
+
 int pntf_adamw(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, const uint8_t* mask, int64_t n,
                double lr, double beta1, double beta2, double eps, double weight_decay, int64_t step,
                double grad_scale, void* stream) {
@@ -429,15 +435,15 @@ int pntf_adamw(float* params, const float* grads, float* exp_avg, float* exp_avg
   return launch_check("adamw");
 }
 
-int pntf_plan(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta, float thr,
-              int max_iter, int grad_flavour, float* waypoints, int32_t* nsteps, int prec, void* workspace,
-              size_t workspace_bytes, void* stream) {
+static int plan_impl(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta, float thr,
+                     int max_iter, int grad_flavour, int fill_tail, float* waypoints, int32_t* nsteps, int prec,
+                     void* workspace, size_t workspace_bytes, void* stream) {
   if (int rc = check_common(params, B, start_goal, 1, Q, d)) return rc;
   if (!waypoints || !nsteps || max_iter < 0) return fail(PNTF_ERR_ARG, "bad plan argument");
   if (int rc = check_prec(prec)) return rc;
   if (Q == 0) return PNTF_OK;
   if (prec == PNTF_PREC_TC)
-    return tc_plan(params, B, start_goal, Q, d, eta, thr, max_iter, grad_flavour, waypoints, nsteps, workspace,
+    return tc_plan(params, B, start_goal, Q, d, eta, thr, max_iter, grad_flavour, fill_tail, waypoints, nsteps, workspace,
                    workspace_bytes, stream);
   if (!workspace || workspace_bytes < kPackedBytes) return fail(PNTF_ERR_WORKSPACE, "workspace too small");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -450,6 +456,7 @@ int pntf_plan(const float* params, const float* B, const float* start_goal, int6
   a.n_total = Q; a.n_per_env = Q; a.pair_begin = 0; a.pair_count = Q;
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
   pa.eta = eta; pa.thr = thr; pa.max_iter = max_iter; pa.waypoints = waypoints; pa.nsteps = nsteps;
+  pa.fill_tail = fill_tail;
   const int P = tile_pairs(d);
   const int64_t ntiles = (Q + P - 1) / P;
   // more CTAs than SMs do not help (1 CTA/SM); tiles are handed out round-robin
@@ -466,6 +473,20 @@ int pntf_plan(const float* params, const float* B, const float* start_goal, int6
   }
   prof_stop(s);
   return launch_check("simt_plan");
+}
+
+int pntf_plan(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta, float thr,
+              int max_iter, int grad_flavour, float* waypoints, int32_t* nsteps, int prec, void* workspace,
+              size_t workspace_bytes, void* stream) {
+  return plan_impl(params, B, start_goal, Q, d, eta, thr, max_iter, grad_flavour, 1, waypoints, nsteps, prec, workspace,
+                   workspace_bytes, stream);
+}
+
+int pntf_plan_compact(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta, float thr,
+                      int max_iter, int grad_flavour, float* waypoints, int32_t* nsteps, int prec, void* workspace,
+                      size_t workspace_bytes, void* stream) {
+  return plan_impl(params, B, start_goal, Q, d, eta, thr, max_iter, grad_flavour, 0, waypoints, nsteps, prec, workspace,
+                   workspace_bytes, stream);
 }
 
 }  // extern "C"

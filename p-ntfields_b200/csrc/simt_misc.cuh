@@ -88,6 +88,7 @@ struct PlanArgs {
   int max_iter;
   float* waypoints;     // [Q][max_iter+2][2D]
   int32_t* nsteps;      // [Q]
+  int fill_tail;        // 1: rows after the last step repeat the final position; 0: left untouched
 };
 
 template <int D>
@@ -145,7 +146,7 @@ __global__ void __launch_bounds__(kThreads, 1) simt_plan_kernel(const PlanArgs p
     for (int p = 0; p < P; ++p) {
       if (!ts.valid[p]) continue;
       const int64_t base = (pair0 + p) * wstride;
-      const int first = (steps[p] + 1) * 2 * D, last = (pa.max_iter + 2) * 2 * D;
+      const int first = (steps[p] + 1) * 2 * D, last = pa.fill_tail ? (pa.max_iter + 2) * 2 * D : 0;
       for (int e = first + threadIdx.x; e < last; e += kThreads) pa.waypoints[base + e] = ts.x[p][e % (2 * D)];
     }
     if (threadIdx.x < P && ts.valid[threadIdx.x]) pa.nsteps[pair0 + threadIdx.x] = steps[threadIdx.x];

@@ -41,8 +41,11 @@ int tc_field(int kind, int grad_flavour, const float* params, const float* B, co
              int d, float gamma, float* out, void* workspace, size_t workspace_bytes, void* stream);
 
 int tc_plan(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta, float thr,
-            int max_iter, int grad_flavour, float* waypoints, int32_t* nsteps, void* workspace, size_t workspace_bytes,
-            void* stream);
+            int max_iter, int grad_flavour, int fill_tail, float* waypoints, int32_t* nsteps, void* workspace,
+            size_t workspace_bytes, void* stream);
+
+int tc_debug_adjoint_stats(const void* workspace, size_t workspace_bytes, int E, int64_t N, int d, int layer,
+                           unsigned long long* out, void* stream);
 
 // with_grad = 0: Model.Loss forward; 1: forward + parameter gradients
 int tc_loss(int with_grad, int variant, const float* params, const float* B, const float* coords, const float* speed,

@@ -268,9 +268,12 @@ __host__ __device__ constexpr int act_chunk_off(int k, int nb, int c) {
 constexpr int kActLBO = kAtomBytes;         // between the two 64-row blocks of a feature group
 constexpr int kActSBO = 2 * kAtomBytes;     // between consecutive groups of 8 features
 
+// two floats -> fp16x2 (a in the low half), round to nearest, SATURATING: a magnitude beyond 65504 becomes +-65504
+// instead of inf, so that one out-of-range element cannot turn a whole tile into NaNs in the next product
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
-  __half2 h = __floats2half2_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
 }
 // write 8 consecutive rows (one chunk) of one feature
 __device__ __forceinline__ void st_chunk(uint8_t* tile, int k, int nb, int c, const float* v) {

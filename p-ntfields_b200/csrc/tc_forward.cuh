@@ -62,6 +62,7 @@ struct TcFwdArgs {
   float* waypoints;         // [Q][max_iter+2][2D]
   int32_t* nsteps;          // [Q]
   int* tile_counter;        // zeroed by the host: path queries are handed out to free tile slots dynamically
+  int fill_tail;            // 1: rows after a query's last step repeat the final position (pntf_plan); 0: left untouched
 };
 
 // debug time stamps: slot layout [role][layer][event]
@@ -109,13 +110,13 @@ __device__ __forceinline__ void act_unit(float* y, bool compat) {
       float q = 0.f;
 #pragma unroll
       for (int i = 0; i < D; ++i) q = fmaf(y[1 + e * D + i], y[1 + e * D + i], q);
-      y[1 + NDER + e] = fmaf(q, a.sp, y[1 + NDER + e] * a.s);
+      y[1 + NDER + e] = fmaf(q * kLapScale, a.sp, y[1 + NDER + e] * a.s);
     }
   }
 #pragma unroll
   for (int i = 0; i < NDER; ++i) {
     const float dy = y[1 + i];
-    if constexpr (ORDER == 2) y[1 + NDER + i] = fmaf(dy * dy, a.sp, y[1 + NDER + i] * a.s);
+    if constexpr (ORDER == 2) y[1 + NDER + i] = fmaf(dy * dy * kLapScale, a.sp, y[1 + NDER + i] * a.s);
     if constexpr (ORDER >= 1) y[1 + i] = dy * gate;
   }
 }
@@ -190,7 +191,7 @@ __device__ __forceinline__ void combine_unit(const float* u, const float* w, flo
     const float inv = __fdividef(1.0f, 1.0f + e);
     const float s0 = (dlt >= 0.f) ? inv : e * inv;
     const float s1 = 1.0f - s0;
-    const float q = MAXSIDE ? 10.0f * s0 * s1 : -10.0f * s0 * s1;
+    const float q = (MAXSIDE ? 10.0f * s0 * s1 : -10.0f * s0 * s1) * kLapScale;   // second-order columns are scaled (tc_layers.cuh)
     const float ga = MAXSIDE ? s0 : s1, gb = MAXSIDE ? s1 : s0;   // gates of the start / goal side
     float qa = 0.f, qb = 0.f;
 #pragma unroll
@@ -284,14 +285,14 @@ __device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>
           us[1 + i] = w[i] * cs;
           uc[1 + i] = -w[i] * sn;
           if constexpr (C::ORDER == 2) {
-            us[1 + D + i] = -w[i] * w[i] * sn;
-            uc[1 + D + i] = -w[i] * w[i] * cs;
+            us[1 + D + i] = -w[i] * w[i] * kLapScale * sn;
+            uc[1 + D + i] = -w[i] * w[i] * kLapScale * cs;
           }
           w2 = fmaf(w[i], w[i], w2);
         }
         if constexpr (C::LS) {
-          us[1 + D] = -w2 * sn;
-          uc[1 + D] = -w2 * cs;
+          us[1 + D] = -w2 * kLapScale * sn;
+          uc[1 + D] = -w2 * kLapScale * cs;
         }
       }
     }
@@ -765,8 +766,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
               break;
             }
             // the endpoints already meet: no step; every row repeats the query
-            for (int r = 1; r < nrow; ++r)
-              for (int i = 0; i < 2 * D; ++i) w[int64_t(r) * 2 * D + i] = t0.x[tid][i];
+            if (a.fill_tail)
+              for (int r = 1; r < nrow; ++r)
+                for (int i = 0; i < 2 * D; ++i) w[int64_t(r) * 2 * D + i] = t0.x[tid][i];
             a.nsteps[pair] = 0;
           }
         }
@@ -815,7 +817,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
         for (int k = 0; k < nd; ++k) {
           const Done& r = done[k];
           float* w = a.waypoints + r.q * wstride;
-          const int first_e = (r.steps + 1) * 2 * D, last_e = nrow * 2 * D;
+          const int first_e = (r.steps + 1) * 2 * D, last_e = a.fill_tail ? nrow * 2 * D : 0;
           for (int e = first_e + tid; e < last_e; e += kEpiThreads) w[e] = r.x[e % (2 * D)];
           if (tid == 0) a.nsteps[r.q] = r.steps;
         }
@@ -852,7 +854,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
             const float dy = y[1 + i];
             dtau[i] = dy * o.o1;
             ltau[i] = 0.f;
-            if constexpr (ORDER == 2) ltau[i] = fmaf(dy * dy, o.o2, y[1 + C::N1 + i] * o.o1);
+            if constexpr (ORDER == 2) ltau[i] = fmaf(dy * dy, o.o2, y[1 + C::N1 + i] * kLapUnscale * o.o1);
           }
           if constexpr (C::LS) {
             // summed Laplacian columns: the per-endpoint sums go to the first slot of each endpoint (the residual
@@ -862,7 +864,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
               float q = 0.f;
 #pragma unroll
               for (int i = 0; i < D; ++i) q = fmaf(y[1 + k * D + i], y[1 + k * D + i], q);
-              ltau[k * D] = fmaf(q, o.o2, y[1 + C::N1 + k] * o.o1);
+              ltau[k * D] = fmaf(q, o.o2, y[1 + C::N1 + k] * kLapUnscale * o.o1);
             }
           }
           if (a.tau) a.tau[pair] = tau;

@@ -32,6 +32,17 @@ namespace tc {
 // pntf_forward(LAPLACE) returns per-coordinate columns.
 constexpr int kOrderLapSum = 3;
 
+// The second-order columns travel through the network multiplied by kLapScale.  Their magnitude grows with training
+// (measured: X_13 reaches 6.5e4 = the fp16 maximum after ~150 AdamW steps from random init, scripts/debug_train_nan.py)
+// while the operand tiles are fp16.  Every forward-mode rule is linear in these columns -- L' = s' sum dy^2 + s L, linear
+// layers, combine, output rule -- so carrying Lt = kLapScale * L only means multiplying the quadratic source terms
+// (Fourier, dy^2 s', q a^2) by kLapScale and dividing once in the tail: exact in real arithmetic, free at run time.
+// 2^-10 leaves room up to |L| = 6.7e7; a loss contribution gamma * L (gamma = 1e-3) is negligible long before Lt reaches
+// the fp16 subnormals.  The adjoints of Lt are 1/kLapScale times those of L, which lifts them (they carry a factor gamma)
+// out of the fp16 subnormal range on the way back.
+constexpr float kLapScale = 1.0f / 1024.0f;
+constexpr float kLapUnscale = 1024.0f;
+
 template <int D_, int ORDER_>
 struct TcCfg {
   static constexpr int D = D_, ORDER = ORDER_;

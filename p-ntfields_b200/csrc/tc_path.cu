@@ -269,6 +269,52 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
   return PNTF_OK;
 }
 
+// ---- debug: statistics of the fp16 adjoint tiles Ybar_l a pntf_loss_bwd call left in its workspace (tests only).
+// Adjoints travel as fp16 scaled by kGradScale (tc_reverse.cuh); an overflow (inf) or a flush to zero would otherwise be
+// silent.  out[0] = inf/NaN count, out[1] = subnormal count (0 < |x| < 2^-14), out[2] = nonzero count,
+// out[3] = bits of the largest finite |x| (fp32).
+__global__ void adjoint_stats_kernel(const __half* __restrict__ g, size_t n, unsigned long long* out) {
+  unsigned long long bad = 0, sub = 0, nz = 0;
+  float mx = 0.f;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    const float v = fabsf(__half2float(g[i]));
+    if (!(v <= 65504.f)) { ++bad; continue; }
+    if (v > 0.f) { ++nz; if (v < 6.103515625e-5f) ++sub; }
+    mx = fmaxf(mx, v);
+  }
+  atomicAdd(out + 0, bad);
+  atomicAdd(out + 1, sub);
+  atomicAdd(out + 2, nz);
+  atomicMax(reinterpret_cast<unsigned int*>(out + 3), __float_as_uint(mx));
+}
+
+// layer < 0: all adjoint tiles Ybar_0..12; layer = 100 + l: the forward operand tile X_l (l = 0..13) instead
+int tc_debug_adjoint_stats(const void* workspace, size_t workspace_bytes, int E, int64_t N, int d, int layer,
+                           unsigned long long* out, void* stream) {
+  const size_t P = tc_tile_pairs(d);
+  const size_t ntiles = (size_t(E) * size_t(N) + P - 1) / P;
+  if (workspace_bytes < kImgBytes + ntiles * stash_tile_bytes())
+    return fail(PNTF_ERR_WORKSPACE, "the adjoint statistics need a call that fitted one chunk (%zu tiles)", ntiles);
+  TcStash st{};
+  tc_carve_stash(st, const_cast<uint8_t*>(static_cast<const uint8_t*>(workspace)) + kImgBytes, ntiles);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaMemsetAsync(out, 0, 4 * sizeof(unsigned long long), s);
+  if (e != cudaSuccess) return fail(PNTF_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
+  const uint8_t* base = st.G[0];
+  size_t bytes = 0;
+  if (layer >= 100 && layer <= 113) {
+    base = st.X[layer - 100];
+    bytes = ntiles * size_t(layer_desc(layer - 100).K) * 256;
+  } else if (layer >= 0 && layer <= 12) {
+    base = st.G[layer];
+    bytes = ntiles * size_t(layer_desc(layer).M) * 256;
+  } else {
+    for (int l = 0; l <= 12; ++l) bytes += ntiles * size_t(layer_desc(l).M) * 256;   // G[0] .. G[12] are contiguous
+  }
+  adjoint_stats_kernel<<<4 * sm_count(), 256, 0, s>>>(reinterpret_cast<const __half*>(base), bytes / 2, out);
+  return launch_check("adjoint_stats");
+}
+
 static int tc_check_ws(void* workspace, size_t workspace_bytes, size_t need) {
   if (!workspace || workspace_bytes < need) return fail(PNTF_ERR_WORKSPACE, "workspace too small (%zu < %zu)", workspace_bytes, need);
   if ((reinterpret_cast<uintptr_t>(workspace) & 255) != 0) return fail(PNTF_ERR_ARG, "workspace must be 256-byte aligned");
@@ -329,8 +375,8 @@ int tc_field(int kind, int grad_flavour, const float* params, const float* B, co
 
 // Batched path integration on the tensor cores: first-order forward per step, queries handed out per tile.
 int tc_plan(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta, float thr,
-            int max_iter, int grad_flavour, float* waypoints, int32_t* nsteps, void* workspace, size_t workspace_bytes,
-            void* stream) {
+            int max_iter, int grad_flavour, int fill_tail, float* waypoints, int32_t* nsteps, void* workspace,
+            size_t workspace_bytes, void* stream) {
   if (Q == 0) return PNTF_OK;
   if (int rc = tc_check_ws(workspace, workspace_bytes, align256(kFwdImgBytes) + 256)) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -345,6 +391,7 @@ int tc_plan(const float* params, const float* B, const float* start_goal, int64_
   a.n_total = Q; a.n_per_env = Q; a.pair_begin = 0; a.pair_count = Q;
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
   a.eta = eta; a.thr = thr; a.max_iter = max_iter; a.waypoints = waypoints; a.nsteps = nsteps; a.tile_counter = counter;
+  a.fill_tail = fill_tail;
   const int64_t P = (d == 3) ? TcCfg<3, 1>::P : TcCfg<6, 1>::P;
   const int64_t ntiles = (Q + P - 1) / P;
   const int grid = int(ntiles < sm_count() ? ntiles : sm_count());

@@ -69,8 +69,9 @@ __device__ __forceinline__ void act_adjoint_unit(float* g, const float* x) {
         const float d10 = dxp * t10;          // dy s'
         u = fmaf(dxp * r, d10, u);
         xb = fmaf(gd, d10, xb);
-        g[1 + e * D + i] = fmaf(gd, s, 2.0f * gl * d10);
+        g[1 + e * D + i] = fmaf(gd, s, 2.0f * kLapScale * gl * d10);
       }
+      u *= kLapScale;                           // forward: Lt' = kLapScale s' Q + s Lt
       xb = fmaf(gl, fmaf(u, c2, t10 * (lxp - u)), xb);
       g[1 + NDER + e] = gl * s;
     }
@@ -80,10 +81,10 @@ __device__ __forceinline__ void act_adjoint_unit(float* g, const float* x) {
       const float dxp = x[1 + i], lxp = x[1 + NDER + i];
       const float gd = g[1 + i], gl = g[1 + NDER + i];
       const float d10 = dxp * t10;            // dy s'
-      const float u = dxp * r * d10;          // dy^2 s'
+      const float u = kLapScale * dxp * r * d10;   // kLapScale dy^2 s'
       xb = fmaf(gd, d10, xb);
       xb = fmaf(gl, fmaf(u, c2, t10 * (lxp - u)), xb);
-      g[1 + i] = fmaf(gd, s, 2.0f * gl * d10);
+      g[1 + i] = fmaf(gd, s, 2.0f * kLapScale * gl * d10);
       g[1 + NDER + i] = gl * s;
     }
   }
@@ -153,6 +154,7 @@ __device__ __forceinline__ void combine_adjoint_unit(const float* gmax, const fl
   const float s1 = 1.0f - s0;
   const float q = 10.0f * s0 * s1;
   const float qp = 10.0f * q * (1.0f - 2.0f * s0);
+  const float qL = q * kLapScale, qpL = qp * kLapScale;   // the quadratic sources of the (scaled) second-order columns
   float ub = 0.f;
   if constexpr (C::LS) {
     // summed second-order columns (forward: combine_unit): lmax = [q Qa + A s0 ; q Qb + B s1], lmin = [-q Qa + A s1 ; -q Qb + B s0]
@@ -167,10 +169,10 @@ __device__ __forceinline__ void combine_adjoint_unit(const float* gmax, const fl
       ub += q * ((dmax0 - dmin0) * a - (dmax1 - dmin1) * b);
       qa = fmaf(a, a, qa);
       qb = fmaf(b, b, qb);
-      ou[1 + i] = dmax0 * s0 + dmin0 * s1 + 2.0f * q * a * dl0;
-      ov[1 + i] = dmax1 * s1 + dmin1 * s0 + 2.0f * q * b * dl1;
+      ou[1 + i] = dmax0 * s0 + dmin0 * s1 + 2.0f * qL * a * dl0;
+      ov[1 + i] = dmax1 * s1 + dmin1 * s0 + 2.0f * qL * b * dl1;
     }
-    ub += q * (dl0 * A - dl1 * Bq) + qp * (dl0 * qa + dl1 * qb);
+    ub += q * (dl0 * A - dl1 * Bq) + qpL * (dl0 * qa + dl1 * qb);
     ou[1 + D] = lmax0 * s0 + lmin0 * s1;
     ov[1 + D] = lmax1 * s1 + lmin1 * s0;
   } else {
@@ -181,9 +183,9 @@ __device__ __forceinline__ void combine_adjoint_unit(const float* gmax, const fl
     const float lmax0 = gmax[1 + 2 * D + i], lmax1 = gmax[1 + 3 * D + i];
     const float lmin0 = gmin[1 + 2 * D + i], lmin1 = gmin[1 + 3 * D + i];
     const float dl0 = lmax0 - lmin0, dl1 = lmax1 - lmin1;
-    ub += q * ((dmax0 - dmin0) * a - (dmax1 - dmin1) * b + dl0 * A - dl1 * Bq) + qp * (dl0 * a * a + dl1 * b * b);
-    ou[1 + i] = dmax0 * s0 + dmin0 * s1 + 2.0f * q * a * dl0;
-    ov[1 + i] = dmax1 * s1 + dmin1 * s0 + 2.0f * q * b * dl1;
+    ub += q * ((dmax0 - dmin0) * a - (dmax1 - dmin1) * b + dl0 * A - dl1 * Bq) + qpL * (dl0 * a * a + dl1 * b * b);
+    ou[1 + i] = dmax0 * s0 + dmin0 * s1 + 2.0f * qL * a * dl0;
+    ov[1 + i] = dmax1 * s1 + dmin1 * s0 + 2.0f * qL * b * dl1;
     ou[1 + D + i] = lmax0 * s0 + lmin0 * s1;
     ov[1 + D + i] = lmax1 * s1 + lmin1 * s0;
   }
@@ -437,7 +439,7 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
           for (int i = 0; i < NG; ++i) {
             dtau[i] = y[1 + i] * o.o1;
             ltau[i] = 0.f;
-            if constexpr (!C::LS) ltau[i] = fmaf(y[1 + i] * y[1 + i], o.o2, y[1 + NG + i] * o.o1);
+            if constexpr (!C::LS) ltau[i] = fmaf(y[1 + i] * y[1 + i], o.o2, y[1 + NG + i] * kLapUnscale * o.o1);
           }
           float qs[2] = {0.f, 0.f};
           if constexpr (C::LS) {   // per-endpoint Laplacian sums in the first slot of each endpoint (see tc_forward tail)
@@ -445,7 +447,7 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
             for (int k = 0; k < 2; ++k) {
 #pragma unroll
               for (int i = 0; i < D; ++i) qs[k] = fmaf(y[1 + k * D + i], y[1 + k * D + i], qs[k]);
-              ltau[k * D] = fmaf(qs[k], o.o2, y[1 + NG + k] * o.o1);
+              ltau[k * D] = fmaf(qs[k], o.o2, y[1 + NG + k] * kLapUnscale * o.o1);
             }
           }
           const float y0 = a.alpha * __ldg(a.speed + srow * a.sstride) + 1.0f - a.alpha;
@@ -457,8 +459,8 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
 #pragma unroll
             for (int k = 0; k < 2; ++k) {
               const float lb = lbar[k * D];          // d loss / d lap_k (the same for every coordinate of endpoint k)
-              yb = fmaf(lb, fmaf(qs[k], o.o3, y[1 + NG + k] * o.o2), yb);
-              gy[1 + NG + k] = lb * o.o1;
+              yb = fmaf(lb, fmaf(qs[k], o.o3, y[1 + NG + k] * kLapUnscale * o.o2), yb);
+              gy[1 + NG + k] = lb * o.o1 * kLapUnscale;     // adjoint of the scaled column
 #pragma unroll
               for (int i = 0; i < D; ++i) {
                 const float dy = y[1 + k * D + i];
@@ -471,9 +473,9 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
           for (int i = 0; i < NG; ++i) {
             const float dy = y[1 + i], ly = y[1 + NG + i];
             yb = fmaf(dbar[i] * dy, o.o2, yb);
-            yb = fmaf(lbar[i], fmaf(dy * dy, o.o3, ly * o.o2), yb);
+            yb = fmaf(lbar[i], fmaf(dy * dy, o.o3, ly * kLapUnscale * o.o2), yb);
             gy[1 + i] = fmaf(dbar[i], o.o1, lbar[i] * 2.0f * dy * o.o2);
-            gy[1 + NG + i] = lbar[i] * o.o1;
+            gy[1 + NG + i] = lbar[i] * o.o1 * kLapUnscale;
           }
           }
           gy[0] = yb;

@@ -20,8 +20,8 @@ GRAD_EXACT, GRAD_COMPAT = 0, 1
 OP_FORWARD, OP_LOSS_FWD, OP_LOSS_BWD, OP_PLAN, OP_FIELD = 0, 1, 2, 3, 4
 
 EXPORTS = ["pntf_version", "pntf_last_error", "pntf_param_offset", "pntf_workspace_bytes", "pntf_forward",
-           "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_loss_fwd_gather", "pntf_loss_bwd_gather", "pntf_adamw", "pntf_plan", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end",
-           "pntf_tc_selftest", "pntf_mesh_workspace_bytes", "pntf_mesh_distance"]
+           "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_loss_fwd_gather", "pntf_loss_bwd_gather", "pntf_adamw", "pntf_plan", "pntf_plan_compact", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end",
+           "pntf_tc_selftest", "pntf_mesh_workspace_bytes", "pntf_mesh_distance", "pntf_debug_adjoint_stats"]
 
 _lib = None
 
@@ -55,7 +55,9 @@ def lib():
     c_d = ctypes.c_double
     L.pntf_adamw.argtypes = [c_p, c_p, c_p, c_p, c_p, c_i64, c_d, c_d, c_d, c_d, c_d, c_i64, c_d, c_p]
     L.pntf_plan.argtypes = [c_p, c_p, c_p, c_i64, c_i, c_f, c_f, c_i, c_i, c_p, c_p, c_i, c_p, c_sz, c_p]
+    L.pntf_plan_compact.argtypes = L.pntf_plan.argtypes
     L.pntf_tc_selftest.argtypes = [c_p, c_p, c_p, c_p, c_p]
+    L.pntf_debug_adjoint_stats.argtypes = [c_p, c_sz, c_i, c_i64, c_i, c_i, c_p, c_p]
     L.pntf_mesh_workspace_bytes.restype = c_sz
     L.pntf_mesh_workspace_bytes.argtypes = [c_i64]
     L.pntf_mesh_distance.argtypes = [c_p, c_i64, c_p, c_i64, c_p, c_f, c_f, c_p, c_p, c_sz, c_p]
@@ -220,15 +222,18 @@ def adamw(params, grads, exp_avg, exp_avg_sq, mask, step, lr=1e-3, betas=(0.9, 0
                             float(eps), float(weight_decay), int(step), float(grad_scale), _stream()))
 
 
-def plan(params, B, start_goal, d, eta, thr, max_iter, grad_flavour=GRAD_EXACT, prec=PREC_FP32):
+def plan(params, B, start_goal, d, eta, thr, max_iter, grad_flavour=GRAD_EXACT, prec=PREC_FP32, fill_tail=True):
+    """waypoints[Q, max_iter+2, 2d], nsteps[Q].  fill_tail=False (pntf_plan_compact): rows after nsteps[q] are not
+    written (the buffer is torch.empty: read waypoints[q, :nsteps[q]+1] only)."""
     dev = start_goal.device
     Q = start_goal.shape[0]
     way = torch.empty(Q, max_iter + 2, 2 * d, dtype=torch.float32, device=dev)
     nsteps = torch.zeros(Q, dtype=torch.int32, device=dev)
     ws = workspace(workspace_bytes(OP_PLAN, 1, Q, d, prec), dev)
-    _check(lib().pntf_plan(_ptr(params, name="params"), _ptr(B, name="B"), _ptr(start_goal, name="start_goal"), Q, d,
-                           float(eta), float(thr), int(max_iter), grad_flavour, _ptr(way),
-                           _ptr(nsteps, torch.int32), prec, ws.data_ptr(), ws.numel(), _stream()))
+    fn = lib().pntf_plan if fill_tail else lib().pntf_plan_compact
+    _check(fn(_ptr(params, name="params"), _ptr(B, name="B"), _ptr(start_goal, name="start_goal"), Q, d,
+              float(eta), float(thr), int(max_iter), grad_flavour, _ptr(way),
+              _ptr(nsteps, torch.int32), prec, ws.data_ptr(), ws.numel(), _stream()))
     return way, nsteps
 
 
@@ -244,6 +249,20 @@ def mesh_distance(triangles, points, offset=None, margin=None):
                                     float(offset or 0.0), float(margin or 0.0),
                                     _ptr(speed) if speed is not None else None, ws.data_ptr(), ws.numel(), _stream()))
     return (dist, speed) if speed is not None else dist
+
+
+def adjoint_stats(E, N, d, budget=0, layer=-1):
+    """{inf_nan, subnormal, nonzero, max_abs} of the fp16 adjoint tiles left in the cached workspace by the last
+    loss(..., grad_out=..., prec=PREC_TC) call of the same shape (adjoints carry the library's scale).  layer = -1: all
+    adjoint tiles, 0..12: Ybar_layer, 100 + l: the forward operand tile X_l."""
+    import struct
+    dev = torch.device("cuda", torch.cuda.current_device())
+    ws = workspace(workspace_bytes(OP_LOSS_BWD, E, N, d, PREC_TC, budget), dev)
+    out = torch.zeros(4, dtype=torch.int64, device=dev)
+    _check(lib().pntf_debug_adjoint_stats(ws.data_ptr(), ws.numel(), E, N, d, layer, out.data_ptr(), _stream()))
+    v = out.cpu().tolist()
+    return {"inf_nan": v[0], "subnormal": v[1], "nonzero": v[2],
+            "max_abs": struct.unpack("f", struct.pack("I", v[3] & 0xffffffff))[0]}
 
 
 def tc_selftest(W, X, C):

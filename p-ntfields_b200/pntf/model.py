@@ -13,6 +13,7 @@ import numpy as np
 import torch
 
 from . import capi
+from .dist import gather_rows, shard_rows, world
 from .nn import NN_multi, NN_single, _LossFn, _PREC
 from .params import TENSOR_NAMES
 
@@ -35,17 +36,24 @@ def _default_params(ModelPath, DataPath, device, batch_size):
 class _FusedAdamW:
     """AdamW(lr=1e-3, weight_decay=0.1) on the flat parameter buffer with one fused kernel
     (reference: torch.optim.AdamW, S:954-956 / M:960-962).  Exposes param_groups[0]['lr'] and a
-    torch-shaped state_dict so checkpoints keep the reference's keys."""
+    torch-shaped state_dict so checkpoints keep the reference's keys.
+
+    It reads the flat gradient buffer `fp.grad`, which the parameters' `.grad` alias (nn._NNBase.attach_grads), so
+    whatever was done to `p.grad` between backward() and step() (scaling, clipping) is what gets applied.  One
+    difference from torch.optim.AdamW remains: step() always updates every used parameter -- with an all-zero
+    gradient buffer (no backward() since zero_grad()) that is a pure weight-decay / moment-decay step, where torch
+    skips parameters whose .grad is None."""
 
     def __init__(self, network, lr=1e-3, weight_decay=0.1, betas=(0.9, 0.999), eps=1e-8):
         self.network = network
         self.param_groups = [{'lr': lr, 'weight_decay': weight_decay, 'betas': betas, 'eps': eps}]
-        fp = network.flat()
+        fp = network.flat(require_cuda=False)
         self.exp_avg = torch.zeros_like(fp.flat)
         self.exp_avg_sq = torch.zeros_like(fp.flat)
         self.step_count = 0
 
-    def zero_grad(self):
+    def zero_grad(self, set_to_none=False):
+        """Zeroes the flat gradient buffer (the parameters' .grad are views of it and stay attached)."""
         self.network.flat().grad.zero_()
 
     def step(self, grad_scale=1.0):
@@ -56,7 +64,7 @@ class _FusedAdamW:
                    betas=g['betas'], eps=g['eps'], weight_decay=g['weight_decay'], grad_scale=grad_scale)
 
     def state_dict(self):
-        fp = self.network.flat()
+        fp = self.network.flat(require_cuda=False)
         state = {}
         idx = 0
         for k in TENSOR_NAMES:
@@ -104,13 +112,20 @@ class _ModelBase:
     def load_pretrained_state_dict(self, state_dict):
         own_state = self.state_dict  # noqa: F841  (kept: the reference defines this stub, S:1165-1166)
 
+    def _loss_eval(self, pts, yo, B, E, N, beta, gamma):
+        """Loss() under torch.no_grad(): forward-only kernels (no stash, no parameter gradients)."""
+        net = self.network
+        loss_out, diff = capi.loss(self.variant, net.flat().flat, B, pts, yo, E, N, self.dim, 1.0, float(beta),
+                                   float(gamma), prec=_PREC[net.precision])
+        return loss_out[0], loss_out[1], diff
+
     # -- shared pieces of the trainer ------------------------------------------------------------------
     def _loss_step(self, coords, speed, B, E, N, alpha, beta, gamma):
         """Fused loss + gradient into the flat grad buffer; returns the device tensor [loss, loss_n]."""
         fp = self.network.flat()
         loss_out, _ = capi.loss(self.variant, fp.flat, B, coords, speed, E, N, self.dim, alpha, beta, gamma,
                                 grad_out=fp.grad, prec=_PREC[self.network.precision],
-                                budget=self.network.stash_budget)
+                                budget=self.network.stash_budget, loss_out=fp.loss_slot)
         return loss_out
 
     def _loss_step_gather(self, table, index, B, E, N, alpha, beta, gamma):
@@ -118,25 +133,51 @@ class _ModelBase:
         fp = self.network.flat()
         loss_out, _ = capi.loss_gather(self.variant, fp.flat, B, table, index, E, N, self.dim, alpha, beta, gamma,
                                        grad_out=fp.grad, prec=_PREC[self.network.precision],
-                                       budget=self.network.stash_budget)
+                                       budget=self.network.stash_budget, loss_out=fp.loss_slot,
+                                       diff=self._diff_buffer(E * N))
         return loss_out
 
-    def plan(self, start_goal, B=None, step=0.03, thr=0.06, max_iter=500, grad_mode=None):
+    def _diff_buffer(self, n):
+        buf = getattr(self, "_diff_buf", None)
+        if buf is None or buf.numel() < n or buf.device != self._dev():
+            buf = torch.empty(n, dtype=torch.float32, device=self._dev())
+            self._diff_buf = buf
+        return buf[:n]
+
+    # -- query sharding: planning and inference split their rows over the ranks of an initialised
+    # torch.distributed group, one contiguous slice per rank (dist.shard_range), no collective.  shard=True returns this
+    # rank's rows only; gather=True additionally all-gathers them so that every rank holds the whole result.
+    def _rows(self, t, shard):
+        if shard and world()[1] > 1:
+            return shard_rows(t)[0]
+        return t
+
+    def _out(self, local, n_total, shard, gather):
+        if shard and gather and world()[1] > 1:
+            return gather_rows(local, n_total)
+        return local
+
+    def plan(self, start_goal, B=None, step=0.03, thr=0.06, max_iter=500, grad_mode=None, fill_tail=True, shard=False,
+             gather=False):
         """Batched bidirectional path integration (test/gib_plan.py:53-97, test/arm_plan.py:111-158).
 
         start_goal[Q,2d] -> (waypoints[Q,max_iter+2,2d], nsteps[Q]); waypoints[q,:nsteps[q]+1,:d] is the
         start-side trajectory, waypoints[q,:nsteps[q]+1,d:] the goal-side one (``path()`` joins them).
-        grad_mode: 'exact' or 'compat' (default: what the reference model uses -- see Gradient)."""
+        grad_mode: 'exact' or 'compat' (default: what the reference model uses -- see Gradient).
+        fill_tail=False: rows after nsteps[q] are left unwritten (30x fewer bytes at the reference's cap of 500).
+        shard / gather: split the queries over the ranks of torch.distributed (see above)."""
         if grad_mode is None:
             grad_mode = self.default_grad_mode
         if B is None:
             B = self.B if self.variant == capi.LOSS_MULTI else self.network.B
         dev = self._dev()
-        sg = start_goal.to(device=dev, dtype=torch.float32).contiguous()
+        Q = start_goal.shape[0]
+        sg = self._rows(start_goal, shard).to(device=dev, dtype=torch.float32).contiguous()
         Bd = B.to(device=dev, dtype=torch.float32).contiguous()
         flav = capi.GRAD_COMPAT if grad_mode == 'compat' else capi.GRAD_EXACT
-        return capi.plan(self.network.flat().flat, Bd, sg, self.dim, step, thr, max_iter, flav,
-                         prec=_PREC[self.network.precision])
+        way, nst = capi.plan(self.network.flat().flat, Bd, sg, self.dim, step, thr, max_iter, flav,
+                             prec=_PREC[self.network.precision], fill_tail=fill_tail)
+        return self._out(way, Q, shard, gather), self._out(nst, Q, shard, gather)
 
     @staticmethod
     def path(waypoints, nsteps, q, dim):
@@ -156,8 +197,7 @@ class _ModelBase:
             src[0] = -0.25
             src[1] = -0.25
         XP = np.zeros((X.size, 2 * self.dim))
-        XP[:, :self.dim] = src
-        XP[:, self.dim:] = src
+        XP[:, :self.dim] = src                   # goal coordinates beyond the slice plane stay 0 (M:1263-1266)
         XP[:, self.dim + 0] = X.flatten()
         XP[:, self.dim + 1] = Y.flatten()
         XP = torch.tensor(XP, dtype=torch.float32, device=self._dev())
@@ -193,6 +233,8 @@ class Model_single(_ModelBase):
         pts = points.detach().to(device=dev, dtype=torch.float32).contiguous()
         yo = Yobs.detach().to(device=dev, dtype=torch.float32).contiguous()
         B = net.B.to(dtype=torch.float32).contiguous()
+        if not torch.is_grad_enabled():
+            return self._loss_eval(pts, yo, B.view(1, self.dim, -1), 1, pts.shape[0], beta, gamma)
         params = [dict(net.named_parameters())[k] for k in TENSOR_NAMES]
         return _LossFn.apply(net, self.variant, pts, yo, B, 1, pts.shape[0], 1.0, float(beta), float(gamma), *params)
 
@@ -225,30 +267,33 @@ class Model_single(_ModelBase):
         return run_training(self, [data.to(self._dev())], [self.network.B], epochs, log)
 
     # -- inference ---------------------------------------------------------------------------------
-    def _field(self, kind, Xp, gamma=0.0, flavour=capi.GRAD_EXACT):
-        Xp = Xp.detach().to(device=self._dev(), dtype=torch.float32).contiguous()
+    def _field(self, kind, Xp, gamma=0.0, flavour=capi.GRAD_EXACT, shard=False, gather=False):
+        n = Xp.shape[0]
+        Xp = self._rows(Xp.detach(), shard).to(device=self._dev(), dtype=torch.float32).contiguous()
         B = self.network.B.to(dtype=torch.float32).contiguous()
-        return capi.field(kind, self.network.flat().flat, B, Xp, 1, Xp.shape[0], self.dim, gamma, grad_flavour=flavour,
-                          prec=_PREC[self.network.precision])
+        out = capi.field(kind, self.network.flat().flat, B, Xp, 1, Xp.shape[0], self.dim, gamma, grad_flavour=flavour,
+                         prec=_PREC[self.network.precision])
+        return self._out(out, n, shard, gather)
 
-    def TravelTimes(self, Xp):
-        return self._field(capi.FIELD_TRAVEL_TIME, Xp)
+    def TravelTimes(self, Xp, shard=False, gather=False):
+        return self._field(capi.FIELD_TRAVEL_TIME, Xp, shard=shard, gather=gather)
 
-    def Tau(self, Xp):
-        Xp = Xp.to(self._dev())
+    def Tau(self, Xp, shard=False, gather=False):
+        n = Xp.shape[0]
+        Xp = self._rows(Xp, shard).to(self._dev())
         tau, _ = self.network.out(Xp)
-        return tau
+        return self._out(tau, n, shard, gather)
 
-    def Speed(self, Xp):
-        return self._field(capi.FIELD_SPEED, Xp)
+    def Speed(self, Xp, shard=False, gather=False):
+        return self._field(capi.FIELD_SPEED, Xp, shard=shard, gather=gather)
 
-    def Speed2(self, Xp, gamma):
-        return self._field(capi.FIELD_SPEED2, Xp, gamma)
+    def Speed2(self, Xp, gamma, shard=False, gather=False):
+        return self._field(capi.FIELD_SPEED2, Xp, gamma, shard=shard, gather=gather)
 
-    def Gradient(self, Xp):
+    def Gradient(self, Xp, shard=False, gather=False):
         """S:1247-1282.  The reference is only correct for batch 1; this is its row-wise extension
         (identical for one row)."""
-        return self._field(capi.FIELD_DIRECTION, Xp)
+        return self._field(capi.FIELD_DIRECTION, Xp, shard=shard, gather=gather)
 
 
 class Model_multi(_ModelBase):
@@ -273,6 +318,9 @@ class Model_multi(_ModelBase):
         pts = points.detach().to(device=dev, dtype=torch.float32).contiguous().view(E * N, 2 * self.dim)
         yo = Yobs.detach().to(device=dev, dtype=torch.float32).contiguous().view(E * N, 2)
         Bd = B.detach().to(device=dev, dtype=torch.float32).contiguous()
+        if not torch.is_grad_enabled():
+            loss, loss_n, diff = self._loss_eval(pts, yo, Bd, E, N, beta, gamma)
+            return loss, loss_n, diff.view(E, N)
         params = [dict(net.named_parameters())[k] for k in TENSOR_NAMES]
         loss, loss_n, diff = _LossFn.apply(net, self.variant, pts, yo, Bd, E, N, 1.0, float(beta), float(gamma), *params)
         return loss, loss_n, diff.view(E, N)
@@ -304,26 +352,29 @@ class Model_multi(_ModelBase):
         return run_training(self, datas, Bs, epochs, log)
 
     # -- inference (reads self.B like the reference, M:1173-1216) --------------------------------------
-    def _field(self, kind, Xp, B, gamma=0.0, flavour=capi.GRAD_EXACT):
-        Xp = Xp.detach().to(device=self._dev(), dtype=torch.float32).contiguous()
+    def _field(self, kind, Xp, B, gamma=0.0, flavour=capi.GRAD_EXACT, shard=False, gather=False):
+        n = Xp.shape[0]
+        Xp = self._rows(Xp.detach(), shard).to(device=self._dev(), dtype=torch.float32).contiguous()
         Bd = B.detach().to(device=self._dev(), dtype=torch.float32).contiguous()
-        return capi.field(kind, self.network.flat().flat, Bd, Xp, 1, Xp.shape[0], self.dim, gamma, grad_flavour=flavour,
-                          prec=_PREC[self.network.precision])
+        out = capi.field(kind, self.network.flat().flat, Bd, Xp, 1, Xp.shape[0], self.dim, gamma, grad_flavour=flavour,
+                         prec=_PREC[self.network.precision])
+        return self._out(out, n, shard, gather)
 
-    def TravelTimes(self, Xp):
-        return self._field(capi.FIELD_TRAVEL_TIME, Xp, self.B)
+    def TravelTimes(self, Xp, shard=False, gather=False):
+        return self._field(capi.FIELD_TRAVEL_TIME, Xp, self.B, shard=shard, gather=gather)
 
-    def Tau(self, Xp):
-        Xp = Xp.to(self._dev())
+    def Tau(self, Xp, shard=False, gather=False):
+        n = Xp.shape[0]
+        Xp = self._rows(Xp, shard).to(self._dev())
         tau, _ = self.network.out(Xp, self.B)
-        return tau
+        return self._out(tau, n, shard, gather)
 
-    def Speed(self, Xp):
-        return self._field(capi.FIELD_SPEED, Xp, self.B)
+    def Speed(self, Xp, shard=False, gather=False):
+        return self._field(capi.FIELD_SPEED, Xp, self.B, shard=shard, gather=gather)
 
-    def Gradient(self, Xp, B, grad_mode='compat'):
+    def Gradient(self, Xp, B, grad_mode='compat', shard=False, gather=False):
         """M:1218-1248.  grad_mode='compat' (default) reproduces the reference as shipped (its
         out_backgrad evaluates the first encoder gate at softplus(y), M:435-438); 'exact' uses the
         true gradient of tau."""
         flav = capi.GRAD_COMPAT if grad_mode == 'compat' else capi.GRAD_EXACT
-        return self._field(capi.FIELD_DIRECTION, Xp, B, flavour=flav)
+        return self._field(capi.FIELD_DIRECTION, Xp, B, flavour=flav, shard=shard, gather=gather)

@@ -21,26 +21,40 @@ _PREC = {"fp32": capi.PREC_FP32, "tc": capi.PREC_TC}
 
 
 class _LossFn(torch.autograd.Function):
-    """loss = beta * loss_n with gradients w.r.t. the 30 parameter tensors.  The forward call runs
-    pntf_loss_bwd (loss AND parameter gradients in one pass); backward just scales them."""
+    """loss = beta * loss_n with gradients w.r.t. the parameters.
+
+    forward runs pntf_loss_bwd (loss AND d loss / d params in one pass) into a scratch buffer; backward adds
+    ``g * scratch`` to the flat gradient buffer ``fp.grad`` (g = the incoming gradient of `loss`, plus that of
+    `loss_n` divided by beta), which is the buffer the fused optimiser reads and which every parameter's ``.grad``
+    aliases (views).  So ``(2 * loss).backward()``, several backward calls before one ``step()``, gradient clipping on
+    ``p.grad`` and ``zero_grad()`` behave as with the reference's torch.optim.AdamW; no per-step allocation.
+    The parameter inputs receive no autograd gradient of their own (``torch.autograd.grad(loss, params)`` is not
+    supported: read ``p.grad`` after ``backward()``)."""
 
     @staticmethod
     def forward(ctx, net, variant, coords, speed, B, E, N, alpha, beta, gamma, *params):
         fp = net.flat()
-        fp.grad.zero_()
+        tmp = fp.scratch_grad()
+        tmp.zero_()
         loss_out, diff = capi.loss(variant, fp.flat, B, coords, speed, E, N, net.dim, alpha, beta, gamma,
-                                   grad_out=fp.grad, prec=_PREC[net.precision], budget=net.stash_budget)
+                                   grad_out=tmp, prec=_PREC[net.precision], budget=net.stash_budget)
         ctx.net = net
+        ctx.beta = float(beta)
         ctx.mark_non_differentiable(diff)
         return loss_out[0], loss_out[1], diff
 
     @staticmethod
     def backward(ctx, g_loss, g_loss_n, g_diff):
-        fp = ctx.net.flat()
-        grads = []
-        for k in TENSOR_NAMES:
-            grads.append(None if k in UNUSED else fp.grad_views[k] * g_loss)
-        return (None,) * 10 + tuple(grads)
+        net = ctx.net
+        fp = net.flat()
+        g = g_loss
+        if g_loss_n is not None and ctx.beta != 0.0:
+            g = g_loss_n / ctx.beta if g is None else g + g_loss_n / ctx.beta
+        if g is not None:
+            tmp = fp.scratch_grad()
+            fp.grad.addcmul_(tmp, g.to(tmp.dtype).expand_as(tmp))
+        net.attach_grads()
+        return (None,) * (10 + len(TENSOR_NAMES))
 
 
 class _NNBase(torch.nn.Module):
@@ -83,11 +97,13 @@ class _NNBase(torch.nn.Module):
             m.bias.data.uniform_(-stdv, stdv)
 
     # -- flat parameter plumbing -----------------------------------------------------------------
-    def flat(self) -> FlatParams:
-        """The flat parameter buffer the kernels read; parameters are views into it."""
+    def flat(self, require_cuda=True) -> FlatParams:
+        """The flat parameter buffer the kernels read; parameters are views into it.  require_cuda=False is for
+        bookkeeping only (state_dict / checkpoints of a network that lives on the CPU); every compute path asks for
+        a CUDA buffer and raises otherwise: there is no CPU fallback."""
         named = dict(self.named_parameters())
         dev = next(iter(named.values())).device
-        if dev.type != "cuda":
+        if require_cuda and dev.type != "cuda":
             raise RuntimeError("pntf NN needs its parameters on a CUDA device (no CPU fallback); got %s" % dev)
         fp = self._fp
         ok = fp is not None and fp.device == dev
@@ -105,6 +121,17 @@ class _NNBase(torch.nn.Module):
                     named[k].data = fp.views[k]
             self._fp = fp
         return fp
+
+    def attach_grads(self):
+        """Every used parameter's .grad is a view of the flat gradient buffer (encoder1.0.* stays None: the reference
+        never gives it a gradient, S:166 vs S:225)."""
+        fp = self.flat()
+        for k, p in self.named_parameters():
+            if k in UNUSED:
+                continue
+            v = fp.grad_views[k]
+            if p.grad is None or p.grad.data_ptr() != v.data_ptr():
+                p.grad = v
 
     def _run(self, mode, coords, B, E, N, flavour=capi.GRAD_EXACT):
         coords = coords.detach().to(dtype=torch.float32).contiguous()

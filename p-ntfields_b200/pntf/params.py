@@ -42,7 +42,11 @@ class FlatParams:
     def __init__(self, device):
         self.device = torch.device(device)
         self.flat = torch.zeros(capi.PARAM_COUNT, dtype=torch.float32, device=self.device)
-        self.grad = torch.zeros_like(self.flat)
+        # gradient ++ the step's two loss scalars in one buffer: the kernels write both, the data-parallel
+        # all-reduce sends it as one message without packing copies (dist.GradAllReduce.reduce_flat)
+        self.gradbuf = torch.zeros(capi.PARAM_COUNT + 2, dtype=torch.float32, device=self.device)
+        self.grad = self.gradbuf[:capi.PARAM_COUNT]
+        self.loss_slot = self.gradbuf[capi.PARAM_COUNT:]
         self.shapes = tensor_shapes()
         self.offsets = tensor_offsets()
         self.views = OrderedDict()
@@ -56,6 +60,12 @@ class FlatParams:
             o, n = self.offsets[k], int(math.prod(self.shapes[k]))
             mask[o:o + n] = 0
         self.mask = mask.to(self.device)
+
+    def scratch_grad(self):
+        """Scratch gradient of the autograd path (nn._LossFn): forward writes it, backward adds it to `grad`."""
+        if getattr(self, "_scratch", None) is None:
+            self._scratch = torch.zeros(capi.PARAM_COUNT, dtype=torch.float32, device=self.device)
+        return self._scratch
 
     def init_weights(self, generator=None):
         """U(+-2/sqrt(fan_in)) for weights AND biases (models/model_res_sigmoid.py:183-189)."""

@@ -4,11 +4,20 @@ models/model_res_sigmoid_multi.py:953-1141 multi) on the fused kernels.
 Kept from the reference: alpha ramp (0.5 -> cap), beta = 1/mean-diff of the previous epoch,
 gamma = 1e-3, lr clip schedule, 6 steps of 10 000 pairs (per environment) per epoch, the
 5-deep (network, optimiser) snapshot ring and the "loss ratio not in (0, 1.2) -> reload a random
-snapshot and redo the epoch" rule.  Snapshots are device-to-device copies of the flat buffers.
-Under torch.distributed every rank processes its slice of each step's pairs and the flat gradient
-is all-reduced; the rollback decision uses the all-reduced loss and a shared random stream.
+snapshot and redo the epoch" rule, the `/ (len(dataloader) * 5)` normalisation of the multi trainer
+(M:1093-1094, with 6 steps) and `/ len(dataloader)` of the single one (S:1083-1084).  Random draws
+are consumed in the reference's order -- multi: environment order of the epoch (the DataLoader's
+shuffle, M:967-971), then one row permutation per environment of a batch (M:1053-1058); single: one
+row permutation per epoch, applied on top of the previous one (FastTensorDataLoader shuffles in place,
+S:61-64) -- so a recorded reference run can be replayed step by step (`TrainHooks`,
+tests/test_gpu_trainer.py).  Snapshots are device-to-device copies of the flat buffers.
 
-Data feeding: every environment group's tables are stacked once into one
+Under torch.distributed every rank processes its slice of each step's pairs and the flat gradient
+is all-reduced; rank 0's initial weights, Fourier matrices and optimiser state are broadcast first,
+every rank draws the same permutations (same seed), and the rollback decision uses the all-reduced
+loss and a shared random stream, so the replicas stay identical.
+
+Data feeding: all environments' tables are stacked once into one
 GPU-resident [rows, 2d+2] table; a step's batch is an int32 index vector (`perm[lo:hi] + row offset` per
 environment) handed to pntf_loss_bwd_gather, so the reference's per-step `data[perm[lo:hi]]` gather, `stack`
 and `contiguous` copies (M:1053-1066) never materialise.
@@ -19,39 +28,78 @@ import numpy as np
 import torch
 
 from . import capi
-from .dist import GradAllReduce, shard_range, world
+from .dist import GradAllReduce, broadcast_replica_state, shard_range, world
 
 
-def run_training(model, datas, Bs, epochs=None, log=print, inner_batch=10000, steps_per_epoch=6, seed=0):
+class TrainHooks:
+    """Source of the trainer's random draws and observer of its schedule.  The default draws from a seeded
+    generator; tests substitute recorded draws of a reference run and collect the per-step / per-epoch records."""
+
+    def __init__(self, seed=0, device="cpu"):
+        self.rng = random.Random(seed)                       # identical on every rank
+        self.gen = torch.Generator(device=device)
+        self.gen.manual_seed(seed)
+        self.device = device
+
+    def randperm(self, n):
+        return torch.randperm(n, device=self.device, generator=self.gen)
+
+    def rollback_index(self):
+        return self.rng.randint(0, 4)                        # S:1093 / M:1104
+
+    def on_step(self, rec):
+        pass
+
+    def on_epoch(self, rec):
+        pass
+
+
+def lr_schedule(epoch):
+    """S:1039 / M:1025."""
+    return float(np.clip(1e-3 * (1 - (epoch - 8000) / 1000.), a_min=5e-4, a_max=1e-3))
+
+
+def run_training(model, datas, Bs, epochs=None, log=print, inner_batch=10000, steps_per_epoch=6, seed=0, hooks=None):
     multi = model.variant == capi.LOSS_MULTI
     net, opt = model.network, model.optimizer
     fp = net.flat()
     dev = fp.device
-    d = model.dim
     rank, ws = world()
     n_epochs = int(epochs if epochs is not None else model.Params['Training']['Number of Epochs'])
-    rng = random.Random(seed)                    # identical on every rank
-    gen = torch.Generator(device=dev)
-    gen.manual_seed(seed)
+    if hooks is None:
+        hooks = TrainHooks(seed, dev)
     reducer = GradAllReduce(capi.PARAM_COUNT, dev)
+    Bs = [b.to(device=dev, dtype=torch.float32).contiguous() for b in Bs]
+    if ws > 1:
+        # replicas must start from the same weights / Fourier matrices / optimiser state (each rank drew its own)
+        broadcast_replica_state([fp.flat, opt.exp_avg, opt.exp_avg_sq] + Bs, opt)
+        if not multi:
+            net.B = Bs[0]                        # [d, 128] as NN_single stores it (S:139)
+            model.B = Bs[0].T
 
+    n_env = len(datas)
     env_batch = int(model.Params['Training']['Batch Size']) if multi else 1
-    groups = [list(range(i, min(i + env_batch, len(datas)))) for i in range(0, len(datas), env_batch)]
+    rows = int(datas[0].shape[0])                # M:997: rows of the first environment
     if multi:
-        n_loader = len(groups)
+        n_loader = -(-n_env // env_batch)
         norm = n_loader * 5.0                    # M:1093-1094 divides by len(dataloader)*5 with 6 steps
+        steps = min(int(rows / inner_batch), steps_per_epoch)
     else:
-        n_loader = int(np.ceil(datas[0].shape[0] / inner_batch))
+        inner_batch = int(model.Params['Training']['Batch Size'])
+        n_loader = -(-rows // inner_batch)
         norm = float(n_loader)                   # S:1083-1084
+        steps = min(n_loader, steps_per_epoch)
+    if steps < 1:
+        raise RuntimeError("the dataset has %d rows per environment, fewer than one batch of %d" % (rows, inner_batch))
+    if inner_batch < ws:
+        raise RuntimeError("a batch of %d pairs cannot be split over %d ranks" % (inner_batch, ws))
 
-    # GPU-resident tables, one per environment group (rows of the group's environments stacked)
-    tables = []
-    for grp in groups:
-        tabs = [datas[e].to(device=dev, dtype=torch.float32) for e in grp]
-        offs = [0]
-        for t in tabs:
-            offs.append(offs[-1] + t.shape[0])
-        tables.append((torch.cat(tabs).contiguous(), offs))
+    # one GPU-resident table: the environments' rows stacked (row offset per environment)
+    offs = [0]
+    for t in datas:
+        offs.append(offs[-1] + int(t.shape[0]))
+    table = torch.cat([t.to(device=dev, dtype=torch.float32) for t in datas]).contiguous()
+    single_order = None                          # single: the loader's cumulative in-place shuffle (S:61-64)
 
     beta, current_diff, step = 1.0, 1.0, -2000.0 / 4000.0
     snap = lambda: (fp.flat.clone(), opt.snapshot())
@@ -66,50 +114,77 @@ def run_training(model, datas, Bs, epochs=None, log=print, inner_batch=10000, st
         if len(queue) > 5:
             queue.pop(0)
         current_state = snap()
-        opt.param_groups[0]['lr'] = float(np.clip(1e-3 * (1 - (epoch - 8000) / 1000.), a_min=5e-4, a_max=1e-3))
+        opt.param_groups[0]['lr'] = lr_schedule(epoch)
         prev_diff = current_diff
+        repeats = 0
         while True:
             totals = torch.zeros(2, dtype=torch.float32, device=dev)
-            order = list(range(len(groups)))
-            rng.shuffle(order)
-            for gi in order:
-                grp = groups[gi]
+            if multi:
+                env_order = [int(e) for e in hooks.randperm(n_env).tolist()]
+                batches = [env_order[i:i + env_batch] for i in range(0, n_env, env_batch)]
+            else:
+                batches = [[0]]
+            last_B = None
+            for grp in batches:
                 E = len(grp)
-                Ns = min(datas[e].shape[0] for e in grp)
-                perms = [torch.randperm(Ns, device=dev, generator=gen) for _ in grp]
-                B = torch.stack([Bs[e].to(torch.float32) for e in grp]).contiguous()
-                nsteps = min(int(Ns / inner_batch), steps_per_epoch) if multi else min(n_loader, steps_per_epoch)
-                for ii in range(max(nsteps, 1)):
-                    lo, hi = ii * inner_batch, min((ii + 1) * inner_batch, Ns)
-                    b, e_ = shard_range(hi - lo, rank, ws)
-                    table, offs = tables[gi]
+                if multi:
+                    perms = [hooks.randperm(rows).to(dev) for _ in grp]
+                else:
+                    r = hooks.randperm(rows).to(dev)
+                    single_order = r if single_order is None else single_order[r]
+                    perms = [single_order]
+                B = torch.stack([Bs[e] for e in grp]).contiguous()
+                last_B = Bs[grp[0]]              # M:1069: self.B = B[0, :]
+                # 0.01 |B|^2 of the multi loss (M:947) enters every rank's loss_n once: taken out ws-1 times below
+                b_term = 0.01 * float((B.double() ** 2).sum().item()) if (multi and ws > 1) else 0.0
+                for ii in range(steps):
+                    lo, hi = ii * inner_batch, min((ii + 1) * inner_batch, rows)
+                    n_g = hi - lo
+                    b, e_ = shard_range(n_g, rank, ws)
                     n = e_ - b
-                    index = torch.cat([perms[j][lo + b:lo + e_] + offs[j] for j in range(E)]).to(torch.int32)
+                    # a rank's loss and gradient are means over ITS n pairs; weighting them by n ws / n_g makes the
+                    # all-reduced sum / ws the mean over the step's n_g pairs whatever the shard sizes (w = 1 when equal)
+                    w = n * ws / float(n_g)
                     fp.grad.zero_()
-                    loss_out = model._loss_step_gather(table, index, B, E, n, alpha, beta, gamma)
-                    _, loss_out = reducer(fp.grad, loss_out)
+                    if n > 0:
+                        index = torch.cat([perms[j][lo + b:lo + e_] + offs[grp[j]] for j in range(E)]).to(torch.int32)
+                        model._loss_step_gather(table, index, B, E, n, alpha, beta * w, gamma)
+                        if w != 1.0:
+                            fp.loss_slot[1:].mul_(w)
+                    else:
+                        index = None
+                        fp.loss_slot.zero_()
+                    _, loss_out = reducer.reduce_flat(fp)
+                    if b_term != 0.0:
+                        corr = (ws - 1) * b_term / (E * n_g)
+                        loss_out = loss_out - torch.tensor([beta * corr, corr], dtype=torch.float32, device=dev)
                     opt.step(grad_scale=1.0 / ws)
                     totals += loss_out
+                    hooks.on_step({"epoch": epoch, "step": ii, "envs": list(grp), "alpha": alpha, "beta": beta,
+                                   "gamma": gamma, "lr": opt.param_groups[0]['lr'], "loss_out": loss_out, "index": index})
             totals /= norm
             total_train_loss, total_diff = totals[0].item(), totals[1].item()
             current_diff = total_diff
             ratio = current_diff / prev_diff
             if 0 < ratio < 1.2:
                 break
-            k = rng.randint(0, 4)
+            repeats += 1
+            k = hooks.rollback_index()
             k = min(k, len(queue) - 1)        # the reference indexes past the ring before 5 epochs exist
             fp.flat.copy_(queue[k][0])
             opt.restore(queue[k][1])
             log("RepeatEpoch = {} -- Loss = {:.4e} -- Alpha = {:.4e}".format(epoch, total_diff, alpha))
         model.total_train_loss.append(total_train_loss)
+        hooks.on_epoch({"epoch": epoch, "alpha": alpha, "beta": beta, "gamma": gamma, "lr": opt.param_groups[0]['lr'],
+                        "total_diff": total_diff, "total_train_loss": total_train_loss, "repeats": repeats})
         beta = 1.0 / total_diff
         history.append((epoch, total_diff, alpha))
         if rank == 0 and epoch % model.Params['Training']['Print Every * Epoch'] == 0:
             log("Epoch = {} -- Loss = {:.4e} -- Alpha = {:.4e}".format(epoch, total_diff, alpha))
+        if multi:
+            model.B = last_B
         if rank == 0 and model.Params['ModelPath'] and (
                 epoch % model.Params['Training']['Save Every * Epoch'] == 0 or epoch == n_epochs or epoch == 1):
-            if multi:
-                model.B = Bs[groups[order[-1]][0]]
             try:
                 model.plot(epoch, total_diff, alpha)
                 model.save(epoch=epoch, val_loss=total_diff)

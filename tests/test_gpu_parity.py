@@ -293,7 +293,7 @@ def test_training_loop_reduces_loss(capi):
     d = 3
     envs = []
     for e in range(2):
-        c, s = synth.sample_pairs(4096, d, DEV, seed=10 + e, margin=0.5 / 5)
+        c, s = synth.sample_pairs(10000, d, DEV, seed=10 + e, margin=0.5 / 5)     # one step of 2 x 10 000 pairs per epoch
         envs.append((torch.cat([c, s], dim=1), synth.sample_B(d, DEV, seed=20 + e)[0]))
     model = M.Model("", "", d, 2, device=DEV)
     hist = model.train(envs=envs, epochs=6, log=lambda *a: None)
