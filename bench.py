@@ -565,7 +565,7 @@ def small_batch_metric(ctx):
     d, rows = 3, 60000
     datas, Bs = [], []
     for e in range(2):
-        c, s = synth.sample_pairs(rows, d, ctx.dev, seed=60 + e, margin=MARGIN["gibson"])
+        c, s = synth.sample_pairs(rows, d, ctx.dev, seed=60 + e, margin=MARGIN["test"], near_obstacle=True)
         datas.append(torch.cat([c, s], dim=1))
         Bs.append(synth.sample_B(d, ctx.dev, seed=70 + e, E=1)[0])
     torch.manual_seed(0)

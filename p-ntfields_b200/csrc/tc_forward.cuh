@@ -63,6 +63,7 @@ struct TcFwdArgs {
   int32_t* nsteps;          // [Q]
   int* tile_counter;        // zeroed by the host: path queries are handed out to free tile slots dynamically
   int fill_tail;            // 1: rows after a query's last step repeat the final position (pntf_plan); 0: left untouched
+  int coords_bulk;          // 1: dense, 16-byte aligned coordinates -> a tile's P x 2D floats arrive by one bulk copy (TMA)
 };
 
 // debug time stamps: slot layout [role][layer][event]
@@ -316,6 +317,7 @@ struct TcCtl {
   uint64_t go;                  // completes once per announcement
   volatile int more;            // 1 = another pass follows, 0 = the CTA is done
   uint32_t ready;               // PNTF_HELPER_POLL: weight stages landed so far (written by the helper thread)
+  uint64_t cbar[2];             // coordinates of the tile in ts[i] have landed (one completion per load_tile call)
 };
 
 // all epilogue threads (converged warps): half h of the next operand tile (and its TMEM pre-loads) is complete.
@@ -447,7 +449,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
   uint8_t* act = smem;                        // two operand-tile buffers: X_l in buffer l & 1
   uint8_t* ring = smem + 2 * kTileBytes;
   __shared__ TcCtl<S> ctl;
-  __shared__ TcTile<C> ts[2];
+  __shared__ __align__(16) TcTile<C> ts[2];
   __shared__ float y13s[2][kRows];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane_id = tid & 31;
@@ -460,6 +462,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     for (int i = 0; i < 4; ++i) mbar_init(&ctl.sd[i >> 1][i & 1], 1);
     for (int i = 0; i < 4; ++i) mbar_init(&ctl.xio[i >> 1][i & 1], 1);
     mbar_init(&ctl.go, 1);
+    mbar_init(&ctl.cbar[0], 1);
+    mbar_init(&ctl.cbar[1], 1);
     ctl.ready = 0;
     fence_barrier_init();
   }
@@ -599,18 +603,36 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     uint32_t nar0 = 0, nar1 = 0;
     const bool compat = a.compat != 0;
     // coordinates of the CTA's first two tiles (later tiles are fetched two tiles ahead by the tail threads)
-    auto load_tile = [&](int64_t tile, TcTile<C>& t) {
-      const int64_t pair = a.pair_begin + tile * P + tid;
-      const bool valid = tile < ntiles && pair < a.pair_begin + a.pair_count && pair < a.n_total;
+    // Called by threads tid < P.  Dense input (coords_bulk) and a full tile: the tile's P x 2D floats are contiguous in
+    // global memory and in ts[i].x, so thread 0 fetches them with ONE bulk copy (cp.async.bulk, completion on cbar[i]);
+    // ragged last tile / gathered batches (pntf_loss_*_gather): per-thread loads.  Either way cbar[i] completes once.
+    static_assert(sizeof(TcTile<C>) % 16 == 0 && (P * 2 * D * sizeof(float)) % 16 == 0, "bulk copies move 16-byte units");
+    auto load_tile = [&](int64_t tile, int i) {
+      TcTile<C>& t = ts[i];
+      const int64_t first = a.pair_begin + tile * P;
+      const int64_t pair = first + tid;
+      const int64_t end = (a.pair_begin + a.pair_count < a.n_total) ? a.pair_begin + a.pair_count : a.n_total;
+      const bool valid = tile < ntiles && pair < end;
+      const bool bulk = a.coords_bulk != 0 && tile < ntiles && first + P <= end;
       t.valid[tid] = valid;
       t.env[tid] = valid ? int(pair / a.n_per_env) : 0;
+      if (bulk) {
+        if (tid == 0) {
+          fence_proxy_async();   // earlier generic-proxy reads of ts[i].x are ordered before the async-proxy write
+          mbar_arrive_expect_tx(&ctl.cbar[i], uint32_t(P * 2 * D * sizeof(float)));
+          bulk_g2s(&t.x[0][0], a.coords + first * 2 * D, uint32_t(P * 2 * D * sizeof(float)), &ctl.cbar[i]);
+        }
+      } else {
 #pragma unroll
-      for (int i = 0; i < 2 * D; ++i) t.x[tid][i] = valid ? __ldg(a.coords + src_row(a, pair) * a.cstride + i) : 0.f;
+        for (int k = 0; k < 2 * D; ++k) t.x[tid][k] = valid ? __ldg(a.coords + src_row(a, pair) * a.cstride + k) : 0.f;
+        if (tid == 0) mbar_arrive(&ctl.cbar[i]);
+      }
     };
+    uint32_t ncb[2] = {0, 0};
     if constexpr (!PLAN) {
       if (tid < P) {
-        load_tile(blockIdx.x, ts[0]);
-        load_tile(int64_t(blockIdx.x) + gridDim.x, ts[1]);
+        load_tile(blockIdx.x, 0);
+        load_tile(int64_t(blockIdx.x) + gridDim.x, 1);
       }
       named_bar_sync(1, kEpiThreads);
     }
@@ -635,6 +657,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
         PNTF_WAIT_SD1();
         PNTF_WAIT_SD1();
       }
+      if constexpr (!PLAN) { mbar_wait(&ctl.cbar[par], ncb[par] & 1); ++ncb[par]; }   // this tile's coordinates have landed
       fourier_tile<C>(a, ts[par], buf0);
       PNTF_PUB(0);
       PNTF_PUB(1);
@@ -896,9 +919,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
           }
           }
         }
-        // this buffer's next user is the tile after next: fetch its coordinates now (the barrier of the
-        // next tile orders these writes before its readers)
-        load_tile(tile + 2 * int64_t(gridDim.x), ts[par]);
+        // this buffer's next user is the tile after next: fetch its coordinates now (the barrier of the next tile
+        // orders per-thread writes before its readers; a bulk copy overwrites every row, so the P tail threads first
+        // agree that all of them are done reading)
+        if constexpr (P <= 32) __syncwarp((P == 32) ? 0xffffffffu : ((1u << (P & 31)) - 1u));
+        else named_bar_sync(2, P);
+        load_tile(tile + 2 * int64_t(gridDim.x), par);
       }
     }
 #undef PNTF_WAIT_ACC0

@@ -77,11 +77,7 @@ def test_single_reader_layout(tmp_path):
 
 @pytest.mark.skipif(not os.path.isdir(REF), reason="needs the reference checkout (build container)")
 def test_readers_agree_with_the_reference_loaders(tmp_path):
-    sys.path.insert(0, REF)
-    try:
-        from models import data_multi, data_mlp
-    finally:
-        sys.path.remove(REF)
+    data_multi, data_mlp = _import_reference(("data_multi", "data_mlp"))
     envs = [train_fixture_env(200 + i, 40, 3) for i in range(3)]
     root = str(tmp_path / "m") + "/"
     write_multi_dataset(root, envs)
@@ -118,21 +114,24 @@ def test_reference_written_checkpoint_loads(tmp_path):
     assert ck["epoch"] == 3 and tuple(ck["B_state_dict"].shape) == (3, 128)
 
 
-def _import_reference():
+def _import_reference(names=("model_res_sigmoid", "model_res_sigmoid_multi")):
+    """Modules of the reference's `models` package, imported in isolation from the repo's drop-in package of the same
+    name (2-module shim: empty matplotlib / matplotlib.pylab, pickle5 -> pickle)."""
+    import importlib
     for name in ("matplotlib", "matplotlib.pylab"):
         sys.modules.setdefault(name, types.ModuleType(name))
     sys.modules.setdefault("pickle5", pickle)
     saved = {k: sys.modules.pop(k) for k in list(sys.modules) if k == "models" or k.startswith("models.")}
     sys.path.insert(0, REF)
     try:
-        from models import model_res_sigmoid as S, model_res_sigmoid_multi as M
+        mods = tuple(importlib.import_module("models." + n) for n in names)
     finally:
         sys.path.remove(REF)
         for k in list(sys.modules):
             if k == "models" or k.startswith("models."):
                 del sys.modules[k]
         sys.modules.update(saved)
-    return S, M
+    return mods
 
 
 @pytest.mark.skipif(not os.path.isdir(REF), reason="needs the reference checkout (build container)")
