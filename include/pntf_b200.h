@@ -127,6 +127,19 @@ int pntf_plan(const float* params, const float* B, const float* start_goal, int6
               float* waypoints, int32_t* nsteps, int prec,
               void* workspace, size_t workspace_bytes, void* stream);
 
+/* Device-resident schedule (Model.train's epoch, M:1040-1097 / S:1050-1084, replayed as a CUDA graph).
+ * The two calls of a training step with the per-epoch scalars read from DEVICE memory at run time, so that launches
+ * captured once (cudaStreamBeginCapture ... EndCapture on `stream`) stay valid when the host changes the schedule
+ * between replays:  sched[3] = {alpha, beta, gamma} (speed interpolation M:1051, loss weight M:1109, viscosity M:1014),
+ * lr_step[2] = {learning rate M:1025, AdamW step count t as a float}.  Neither call allocates or synchronises. */
+int pntf_loss_bwd_gather_sched(int variant, const float* params, const float* B, const float* dataset, int64_t dataset_rows,
+                               const int32_t* index, int E, int64_t N, int d, const float* sched, float* diff,
+                               float* loss_out, float* grad_params, int prec, void* workspace, size_t workspace_bytes,
+                               void* stream);
+int pntf_adamw_sched(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, const uint8_t* mask, int64_t n,
+                     const float* lr_step, double beta1, double beta2, double eps, double weight_decay, double grad_scale,
+                     void* stream);
+
 /* Same integration; rows of waypoints after a query's last step (row nsteps[q]) are NOT written (the caller's buffer
  * keeps whatever it held).  pntf_plan fills them with the final position, which at the reference's cap of 500 is
  * 30x the bytes of the waypoints themselves; batched callers read waypoints[q, :nsteps[q]+1] only. */

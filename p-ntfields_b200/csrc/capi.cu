@@ -15,6 +15,7 @@ namespace pntf {
 
 static thread_local char g_err[512] = "";
 thread_local PairGather g_gather;
+thread_local const float* g_sched = nullptr;
 static std::atomic<int64_t> g_launches{0};
 
 int fail(int code, const char* fmt, ...) {
@@ -184,6 +185,7 @@ static int loss_bwd_simt(int variant, const float* params, const float* B, const
     carve_stash(a.st, stash_base, D, count_pad);
     b.packed_bwd = packed_b;
     b.wscale = beta / float(double(E) * double(N));
+    b.inv_count = float(1.0 / (double(E) * double(N)));
     const int64_t ntiles = count_pad / C::P;
     const int grid = int(ntiles < sm_count() ? ntiles : sm_count());
     prof_start(KC_FORWARD, s);
@@ -329,7 +331,8 @@ namespace pntf {
 int finalize_loss(int variant, const float* diff, int64_t n_total, const float* B, int E, int d, float beta,
                   float* loss_out, cudaStream_t s) {
   prof_start(KC_FINALIZE, s);
-  loss_finalize_kernel<<<1, 1024, 0, s>>>(diff, n_total, B, E * d * kNumFreq, variant == PNTF_LOSS_MULTI, beta, loss_out);
+  loss_finalize_kernel<<<1, 1024, 0, s>>>(diff, n_total, B, E * d * kNumFreq, variant == PNTF_LOSS_MULTI, beta, g_sched,
+                                          loss_out);
   prof_stop(s);
   return launch_check("loss_finalize");
 }
@@ -408,6 +411,39 @@ int pntf_loss_bwd_gather(int variant, const float* params, const float* B, const
   GatherScope scope(index, 2 * d + 2);
   return pntf_loss_bwd(variant, params, B, dataset, dataset + 2 * d, E, N, d, alpha, beta, gamma, diff, loss_out,
                        grad_params, prec, workspace, workspace_bytes, stream);
+}
+
+// ---- device-resident schedule: an epoch of training steps can be captured in a CUDA graph and replayed
+struct SchedScope {
+  explicit SchedScope(const float* s) { g_sched = s; }
+  ~SchedScope() { g_sched = nullptr; }
+};
+
+int pntf_loss_bwd_gather_sched(int variant, const float* params, const float* B, const float* dataset, int64_t dataset_rows,
+                               const int32_t* index, int E, int64_t N, int d, const float* sched, float* diff,
+                               float* loss_out, float* grad_params, int prec, void* workspace, size_t workspace_bytes,
+                               void* stream) {
+  if (!sched) return fail(PNTF_ERR_ARG, "null schedule");
+  SchedScope scope(sched);
+  return pntf_loss_bwd_gather(variant, params, B, dataset, dataset_rows, index, E, N, d, 1.f, 1.f, 0.f, diff, loss_out,
+                              grad_params, prec, workspace, workspace_bytes, stream);
+}
+
+int pntf_adamw_sched(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, const uint8_t* mask, int64_t n,
+                     const float* lr_step, double beta1, double beta2, double eps, double weight_decay, double grad_scale,
+                     void* stream) {
+  if (!params || !grads || !exp_avg || !exp_avg_sq || !lr_step || n < 0) return fail(PNTF_ERR_ARG, "bad adamw argument");
+  if (n == 0) return PNTF_OK;
+  AdamArgs a{};
+  a.p = params; a.g = grads; a.m = exp_avg; a.v = exp_avg_sq; a.mask = mask; a.n = n;
+  a.omb1 = float(1.0 - beta1); a.b2 = float(beta2); a.omb2 = float(1.0 - beta2); a.eps = float(eps);
+  a.grad_scale = float(grad_scale);
+  a.lr_step = lr_step; a.b1d = beta1; a.b2d = beta2; a.wdd = weight_decay;
+  const int blocks = int((n + 255) / 256 < 4 * sm_count() ? (n + 255) / 256 : 4 * sm_count());
+  prof_start(KC_ADAMW, static_cast<cudaStream_t>(stream));
+  adamw_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  prof_stop(static_cast<cudaStream_t>(stream));
+  return launch_check("adamw(sched)");
 }
 
 int pntf_debug_adjoint_stats(const void* workspace, size_t workspace_bytes, int E, int64_t N, int d, int layer,

@@ -17,6 +17,14 @@ __device__ __forceinline__ int64_t src_row(const A& a, int64_t pair) {
 }
 
 
+// Device-resident schedule (pntf_loss_bwd_gather_sched / pntf_adamw_sched: an epoch of training steps replayed as a
+// CUDA graph): when `sched` is set the kernels read {alpha, beta, gamma} from device memory instead of their launch
+// arguments, so that a captured launch sees the values the host wrote for the current epoch (M:1011-1014, 1109).
+template <class A>
+__device__ __forceinline__ float sched_alpha(const A& a) { return a.sched != nullptr ? __ldg(a.sched) : a.alpha; }
+template <class A>
+__device__ __forceinline__ float sched_gamma(const A& a) { return a.sched != nullptr ? __ldg(a.sched + 2) : a.gamma; }
+
 template <int D>
 struct PairGeom {
   float Dv[D];   // x1 - x0

@@ -27,6 +27,7 @@ struct FwdArgs {
   float* field; int field_kind;           // TAIL_FIELD
   float* diff; int single_variant;        // TAIL_LOSS
   float alpha, gamma;
+  const float* sched;      // optional device-resident {alpha, beta, gamma} (pair_math.cuh)
   int compat;              // derivative gate of the first encoder layer evaluated at softplus(y)
   Stash st;                // training stash (rows are local to this launch)
 };
@@ -259,9 +260,10 @@ __global__ void __launch_bounds__(kThreads, 1) simt_forward_kernel(const FwdArgs
         const float* x = ts.x[threadIdx.x];
         if constexpr (TAIL == TAIL_LOSS && ORDER == 2) {
           const float* sp = a.speed + src_row(a, pair) * a.sstride;
-          const float y0 = a.alpha * __ldg(sp) + 1.0f - a.alpha;
-          const float y1 = a.alpha * __ldg(sp + 1) + 1.0f - a.alpha;
-          a.diff[pair] = eikonal_residual<D, false>(x, tau, dtau, ltau, y0, y1, a.gamma, a.single_variant, 0.f,
+          const float al = sched_alpha(a);
+          const float y0 = al * __ldg(sp) + 1.0f - al;
+          const float y1 = al * __ldg(sp + 1) + 1.0f - al;
+          a.diff[pair] = eikonal_residual<D, false>(x, tau, dtau, ltau, y0, y1, sched_gamma(a), a.single_variant, 0.f,
                                                     nullptr, nullptr, nullptr);
         }
         if constexpr (TAIL == TAIL_FIELD) {

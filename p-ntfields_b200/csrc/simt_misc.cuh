@@ -38,9 +38,24 @@ struct AdamArgs {
   float step_size;    // lr / (1 - b1^t)
   float bc2_sqrt;     // sqrt(1 - b2^t)
   float grad_scale;
+  // optional device-resident {lr, step}: the update constants are then derived on the device (CUDA-graph replay)
+  const float* lr_step;
+  double b1d, b2d, wdd;
 };
 
-__global__ void adamw_kernel(const AdamArgs a) {
+__global__ void adamw_kernel(const AdamArgs a_in) {
+  AdamArgs a = a_in;
+  if (a.lr_step != nullptr) {
+    __shared__ float consts[3];
+    if (threadIdx.x == 0) {
+      const double lr = double(a.lr_step[0]), step = double(a.lr_step[1]);
+      consts[0] = float(1.0 - lr * a.wdd);
+      consts[1] = float(lr / (1.0 - pow(a.b1d, step)));
+      consts[2] = float(sqrt(1.0 - pow(a.b2d, step)));
+    }
+    __syncthreads();
+    a.decay = consts[0]; a.step_size = consts[1]; a.bc2_sqrt = consts[2];
+  }
   for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < a.n; i += int64_t(gridDim.x) * blockDim.x) {
     if (a.mask && a.mask[i] == 0) continue;
     const float g = a.g[i] * a.grad_scale;
@@ -59,7 +74,8 @@ __global__ void adamw_kernel(const AdamArgs a) {
 // (models/model_res_sigmoid.py:930-934, models/model_res_sigmoid_multi.py:946-949).  One block,
 // fixed summation order (deterministic).
 __global__ void loss_finalize_kernel(const float* __restrict__ diff, int64_t n, const float* __restrict__ Bm, int nB,
-                                     int multi, float beta, float* __restrict__ loss_out) {
+                                     int multi, float beta, const float* __restrict__ sched,
+                                     float* __restrict__ loss_out) {
   __shared__ double red[1024];
   double s = 0.0;
   for (int64_t i = threadIdx.x; i < n; i += blockDim.x) s += double(diff[i]);
@@ -74,7 +90,7 @@ __global__ void loss_finalize_kernel(const float* __restrict__ diff, int64_t n, 
   }
   if (threadIdx.x == 0) {
     const float loss_n = float(red[0] / double(n));
-    loss_out[0] = beta * loss_n;
+    loss_out[0] = (sched != nullptr ? sched[1] : beta) * loss_n;
     loss_out[1] = loss_n;
   }
 }

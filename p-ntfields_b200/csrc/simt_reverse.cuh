@@ -14,6 +14,7 @@ struct BwdArgs {
   FwdArgs f;
   const float* packed_bwd;   // packed backward weights
   float wscale;              // d loss / d diff_n  = beta / (E*N)
+  float inv_count;           // 1 / (E*N): with a device-resident schedule wscale = sched[1] * inv_count
 };
 
 // Adjoint of combine_stage.  Inputs: Gb[256][RSG] = adjoint of the combine output (max features
@@ -94,11 +95,12 @@ __global__ void __launch_bounds__(kThreads, 1) simt_reverse_kernel(const BwdArgs
           ltau[i] = fmaf(y[1 + i] * y[1 + i], o.o2, y[1 + NG + i] * o.o1);
         }
         const float* sp = a.speed + src_row(a, pair) * a.sstride;
-        const float y0 = a.alpha * __ldg(sp) + 1.0f - a.alpha;
-        const float y1 = a.alpha * __ldg(sp + 1) + 1.0f - a.alpha;
+        const float al = sched_alpha(a);
+        const float y0 = al * __ldg(sp) + 1.0f - al;
+        const float y1 = al * __ldg(sp + 1) + 1.0f - al;
         float tb, db[NG], lb[NG];
-        const float diff = eikonal_residual<D, true>(ts.x[p], tau, dtau, ltau, y0, y1, a.gamma, a.single_variant,
-                                                     b.wscale, &tb, db, lb);
+        const float diff = eikonal_residual<D, true>(ts.x[p], tau, dtau, ltau, y0, y1, sched_gamma(a), a.single_variant,
+                                                     (a.sched != nullptr ? __ldg(a.sched + 1) * b.inv_count : b.wscale), &tb, db, lb);
         if (a.diff) a.diff[pair] = diff;
         float yb = tb * o.o1;
 #pragma unroll

@@ -16,7 +16,7 @@ void prof_stop(cudaStream_t s);
 int launch_check(const char* what);
 int sm_count();
 int finalize_loss(int variant, const float* diff, int64_t n_total, const float* B, int E, int d, float beta,
-                  float* loss_out, cudaStream_t s);
+                  float* loss_out, cudaStream_t s);   // beta is read from g_sched when that is set
 
 // Batch source of the current call: dense arrays, or rows of a GPU-resident dataset picked by an index array
 // (pntf_loss_*_gather).  Set by the entry point around the call; one host thread per GPU drives the library.
@@ -25,18 +25,15 @@ struct PairGather {
   int row_stride = 0;
 };
 extern thread_local PairGather g_gather;
+// device-resident {alpha, beta, gamma} of the current call (pntf_loss_bwd_gather_sched), else null
+extern thread_local const float* g_sched;
 template <class A>
 inline void apply_gather(A& a, int d) {
+  a.sched = g_sched;
   a.index = g_gather.index;
   a.cstride = g_gather.index ? g_gather.row_stride : 2 * d;
   a.sstride = g_gather.index ? g_gather.row_stride : 2;
 }
-// tensor-core forward: dense, 16-byte aligned coordinates are streamed into shared memory by bulk copies
-template <class A>
-inline void apply_coords_bulk(A& a) {
-  a.coords_bulk = (a.index == nullptr && (reinterpret_cast<uintptr_t>(a.coords) & 15) == 0) ? 1 : 0;
-}
-
 size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes);
 
 int tc_forward(int mode, int grad_flavour, const float* params, const float* B, const float* coords, int E, int64_t N,

@@ -23,6 +23,8 @@ struct TcDwArgs {
   int64_t ntiles;
   float* grad;
   float out_scale;
+  const float* sched;       // optional device-resident {alpha, beta, gamma}: out_scale = sched[1] * inv_scale
+  float inv_scale;
   // fused backward (tc_backward.cuh): wait for flags[tile * 16 + l] == epoch before reading Ybar_l of a tile
   const uint32_t* flags;
   uint32_t epoch;
@@ -115,13 +117,14 @@ __device__ __forceinline__ void tc_dw_role(const TcDwArgs& a, const int cta) {
     const uint32_t lane_base = tmem_base + (uint32_t((warp & 3) * 32) << 16);
     float* dst = a.grad + c_w[l] + size_t(h * 128 + m) * K;
     const bool row_ok = (h * 128 + m) < M;
+    const float sc = a.sched != nullptr ? __ldg(a.sched + 1) * a.inv_scale : a.out_scale;
     const int kc = K / 2;
     for (int c0 = half * kc; c0 < (half + 1) * kc; c0 += 32) {
       float v[32];
       tmem_ld<32>(lane_base + c0, v);
       if (row_ok) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) atomicAdd(dst + c0 + j, v[j] * a.out_scale);
+        for (int j = 0; j < 32; ++j) atomicAdd(dst + c0 + j, v[j] * sc);
       }
     }
   }

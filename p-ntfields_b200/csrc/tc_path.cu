@@ -223,11 +223,11 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     TcFwdArgs& a = r.f;
     a.params = params; a.wimg = fimg; a.B = B; a.coords = coords; a.speed = speed;
     apply_gather(a, D);
-    apply_coords_bulk(a);
     a.n_total = n_total; a.n_per_env = N; a.pair_begin = begin; a.pair_count = count;
     a.diff = diff; a.single_variant = (variant == PNTF_LOSS_SINGLE); a.alpha = alpha; a.gamma = gamma;
     tc_carve_stash(a.st, stash, size_t(tiles));
     r.rimg = rimg; r.grad = grad_params; r.out_scale = out_scale;
+    r.inv_scale = float(1.0 / (double(E) * double(N)) / double(kGradScale));
     const int grid = int(tiles < sm_count() ? tiles : sm_count());
     a.trace = (t0 == 0) ? trace_begin() : nullptr;
     prof_start(KC_TC_FORWARD, s);
@@ -238,6 +238,7 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     if (int rc = launch_check("tc_forward(train)")) return rc;
     TcDwArgs dw{};
     dw.st = a.st; dw.units = units; dw.ntiles = tiles; dw.grad = grad_params; dw.out_scale = out_scale;
+    dw.sched = a.sched; dw.inv_scale = r.inv_scale;
     if (n_dw > 0) {
       // one launch: reverse sweep on the first CTAs, weight gradients trailing it on the last n_dw (tc_backward.cuh)
       uint32_t* flags = stash_flags(a.st, size_t(tiles));
@@ -332,7 +333,6 @@ int tc_forward(int mode, int grad_flavour, const float* params, const float* B, 
   TcFwdArgs a{};
   a.params = params; a.wimg = img; a.B = B; a.coords = coords;
   apply_gather(a, d);
-  apply_coords_bulk(a);
   a.n_total = int64_t(E) * N; a.n_per_env = N; a.pair_begin = 0; a.pair_count = a.n_total;
   a.tau = tau; a.dtau = (mode >= PNTF_MODE_GRAD) ? dtau : nullptr; a.ltau = ltau;
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
@@ -358,7 +358,6 @@ int tc_field(int kind, int grad_flavour, const float* params, const float* B, co
   TcFwdArgs a{};
   a.params = params; a.wimg = img; a.B = B; a.coords = coords;
   apply_gather(a, d);
-  apply_coords_bulk(a);
   a.n_total = int64_t(E) * N; a.n_per_env = N; a.pair_begin = 0; a.pair_count = a.n_total;
   a.field = out; a.field_kind = kind; a.gamma = gamma;
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
@@ -391,7 +390,6 @@ int tc_plan(const float* params, const float* B, const float* start_goal, int64_
   TcFwdArgs a{};
   a.params = params; a.wimg = img; a.B = B; a.coords = start_goal;
   apply_gather(a, d);
-  apply_coords_bulk(a);
   a.n_total = Q; a.n_per_env = Q; a.pair_begin = 0; a.pair_count = Q;
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
   a.eta = eta; a.thr = thr; a.max_iter = max_iter; a.waypoints = waypoints; a.nsteps = nsteps; a.tile_counter = counter;
@@ -434,7 +432,6 @@ int tc_loss(int with_grad, int variant, const float* params, const float* B, con
   TcFwdArgs a{};
   a.params = params; a.wimg = img; a.B = B; a.coords = coords; a.speed = speed;
   apply_gather(a, d);
-  apply_coords_bulk(a);
   a.n_total = int64_t(E) * N; a.n_per_env = N; a.pair_begin = 0; a.pair_count = a.n_total;
   a.diff = diff; a.single_variant = (variant == PNTF_LOSS_SINGLE); a.alpha = alpha; a.gamma = gamma;
   int rc;

@@ -27,6 +27,7 @@ struct TcRevArgs {
   const uint8_t* rimg;      // reverse (transposed) stage images
   float* grad;              // flat parameter gradient (accumulated with atomics)
   float out_scale;          // beta / (E*N) / kGradScale
+  float inv_scale;          // 1 / (E*N) / kGradScale: with a device-resident schedule out_scale = sched[1] * inv_scale
   // Fused backward (tc_backward_kernel): flags[tile * kFlagStride + l] = epoch once Ybar_l of that tile is complete in
   // global memory; the weight-gradient CTAs of the same launch wait on it.  nullptr: separate launches, no flags.
   uint32_t* flags;
@@ -450,10 +451,11 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
               ltau[k * D] = fmaf(qs[k], o.o2, y[1 + NG + k] * kLapUnscale * o.o1);
             }
           }
-          const float y0 = a.alpha * __ldg(a.speed + srow * a.sstride) + 1.0f - a.alpha;
-          const float y1 = a.alpha * __ldg(a.speed + srow * a.sstride + 1) + 1.0f - a.alpha;
+          const float al = sched_alpha(a);
+          const float y0 = al * __ldg(a.speed + srow * a.sstride) + 1.0f - al;
+          const float y1 = al * __ldg(a.speed + srow * a.sstride + 1) + 1.0f - al;
           float tb, dbar[NG], lbar[NG];
-          eikonal_residual<D, true>(x, o.o, dtau, ltau, y0, y1, a.gamma, a.single_variant, kGradScale, &tb, dbar, lbar);
+          eikonal_residual<D, true>(x, o.o, dtau, ltau, y0, y1, sched_gamma(a), a.single_variant, kGradScale, &tb, dbar, lbar);
           float yb = tb * o.o1;
           if constexpr (C::LS) {
 #pragma unroll
@@ -550,7 +552,7 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
     atomicAdd(sdb + kNumBiasSlots + p.lane, dw13);
     // ---- bias gradients (+ output layer weight gradient) of this CTA's tiles
     named_bar_sync(1, kEpiThreads);
-    const float sc = b.out_scale;
+    const float sc = a.sched != nullptr ? __ldg(a.sched + 1) * b.inv_scale : b.out_scale;
     float* gp = b.grad;
     for (int l = 0; l <= 12; ++l) {
       const int M = c_M[l];

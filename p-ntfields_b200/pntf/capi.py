@@ -20,7 +20,7 @@ GRAD_EXACT, GRAD_COMPAT = 0, 1
 OP_FORWARD, OP_LOSS_FWD, OP_LOSS_BWD, OP_PLAN, OP_FIELD = 0, 1, 2, 3, 4
 
 EXPORTS = ["pntf_version", "pntf_last_error", "pntf_param_offset", "pntf_workspace_bytes", "pntf_forward",
-           "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_loss_fwd_gather", "pntf_loss_bwd_gather", "pntf_adamw", "pntf_plan", "pntf_plan_compact", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end",
+           "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_loss_fwd_gather", "pntf_loss_bwd_gather", "pntf_loss_bwd_gather_sched", "pntf_adamw", "pntf_adamw_sched", "pntf_plan", "pntf_plan_compact", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end",
            "pntf_tc_selftest", "pntf_mesh_workspace_bytes", "pntf_mesh_distance", "pntf_debug_adjoint_stats"]
 
 _lib = None
@@ -52,8 +52,11 @@ def lib():
                                        c_sz, c_p]
     L.pntf_loss_bwd_gather.argtypes = [c_i, c_p, c_p, c_p, c_i64, c_p, c_i, c_i64, c_i, c_f, c_f, c_f, c_p, c_p, c_p, c_i,
                                        c_p, c_sz, c_p]
+    L.pntf_loss_bwd_gather_sched.argtypes = [c_i, c_p, c_p, c_p, c_i64, c_p, c_i, c_i64, c_i, c_p, c_p, c_p, c_p, c_i, c_p,
+                                             c_sz, c_p]
     c_d = ctypes.c_double
     L.pntf_adamw.argtypes = [c_p, c_p, c_p, c_p, c_p, c_i64, c_d, c_d, c_d, c_d, c_d, c_i64, c_d, c_p]
+    L.pntf_adamw_sched.argtypes = [c_p, c_p, c_p, c_p, c_p, c_i64, c_p, c_d, c_d, c_d, c_d, c_d, c_p]
     L.pntf_plan.argtypes = [c_p, c_p, c_p, c_i64, c_i, c_f, c_f, c_i, c_i, c_p, c_p, c_i, c_p, c_sz, c_p]
     L.pntf_plan_compact.argtypes = L.pntf_plan.argtypes
     L.pntf_tc_selftest.argtypes = [c_p, c_p, c_p, c_p, c_p]
@@ -212,6 +215,27 @@ def loss_gather(variant, params, B, dataset, index, E, N, d, alpha, beta, gamma,
         _check(lib().pntf_loss_bwd_gather(*common, _ptr(grad_out, name="grad_out"), prec, ws.data_ptr(), ws.numel(),
                                           _stream()))
     return loss_out, diff
+
+
+def loss_gather_sched(variant, params, B, dataset, index, E, N, d, sched, grad_out, diff, loss_out, prec=PREC_TC, budget=0):
+    """loss_gather(..., grad_out=...) with {alpha, beta, gamma} read from the device tensor `sched` (3 floats) at run
+    time: capturable in a CUDA graph (no allocation: every buffer, incl. the cached workspace, must exist already)."""
+    dev = dataset.device
+    ws = workspace(workspace_bytes(OP_LOSS_BWD, E, N, d, prec, budget), dev)
+    _check(lib().pntf_loss_bwd_gather_sched(variant, _ptr(params, name="params"), _ptr(B, name="B"),
+                                            _ptr(dataset, name="dataset"), int(dataset.shape[0]),
+                                            _ptr(index, torch.int32, "index"), E, N, d, _ptr(sched, name="sched"),
+                                            _ptr(diff), _ptr(loss_out), _ptr(grad_out, name="grad_out"), prec,
+                                            ws.data_ptr(), ws.numel(), _stream()))
+
+
+def adamw_sched(params, grads, exp_avg, exp_avg_sq, mask, lr_step, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.1,
+                grad_scale=1.0):
+    """adamw() with {lr, step} read from the device tensor `lr_step` (2 floats) at run time."""
+    _check(lib().pntf_adamw_sched(_ptr(params, name="params"), _ptr(grads, name="grads"), _ptr(exp_avg),
+                                  _ptr(exp_avg_sq), _ptr(mask, torch.uint8, "mask"), params.numel(),
+                                  _ptr(lr_step, name="lr_step"), float(betas[0]), float(betas[1]), float(eps),
+                                  float(weight_decay), float(grad_scale), _stream()))
 
 
 def adamw(params, grads, exp_avg, exp_avg_sq, mask, step, lr=1e-3, betas=(0.9, 0.999), eps=1e-8,

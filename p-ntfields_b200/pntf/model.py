@@ -63,6 +63,14 @@ class _FusedAdamW:
         capi.adamw(fp.flat, fp.grad, self.exp_avg, self.exp_avg_sq, fp.mask, self.step_count, lr=g['lr'],
                    betas=g['betas'], eps=g['eps'], weight_decay=g['weight_decay'], grad_scale=grad_scale)
 
+    def step_sched(self, lr_step, grad_scale=1.0):
+        """step() with {lr, step count} taken from the device tensor lr_step (CUDA-graph replay; the caller advances
+        lr_step[1] on the device and keeps step_count in sync after the replay)."""
+        fp = self.network.flat()
+        g = self.param_groups[0]
+        capi.adamw_sched(fp.flat, fp.grad, self.exp_avg, self.exp_avg_sq, fp.mask, lr_step, betas=g['betas'],
+                         eps=g['eps'], weight_decay=g['weight_decay'], grad_scale=grad_scale)
+
     def state_dict(self):
         fp = self.network.flat(require_cuda=False)
         state = {}

@@ -17,11 +17,19 @@ is all-reduced; rank 0's initial weights, Fourier matrices and optimiser state a
 every rank draws the same permutations (same seed), and the rollback decision uses the all-reduced
 loss and a shared random stream, so the replicas stay identical.
 
+Device-side epoch: one pass over a batch of environments -- its up-to-six steps of
+index build, zero, loss + backward, all-reduce, AdamW and loss accumulation -- is captured ONCE as a CUDA graph
+(`_PassGraph`) and replayed for every later pass; alpha / beta / gamma, the learning rate, the optimiser's step count,
+the row permutations, the environments' table offsets and Fourier matrices live in device buffers the host refreshes
+before a replay (pntf_loss_bwd_gather_sched / pntf_adamw_sched read them at run time), and the pass's losses come back
+in one read.  `graph=False` (or PNTF_TRAIN_GRAPH=0) keeps the launch-by-launch loop; both produce the same numbers.
+
 Data feeding: all environments' tables are stacked once into one
 GPU-resident [rows, 2d+2] table; a step's batch is an int32 index vector (`perm[lo:hi] + row offset` per
 environment) handed to pntf_loss_bwd_gather, so the reference's per-step `data[perm[lo:hi]]` gather, `stack`
 and `contiguous` copies (M:1053-1066) never materialise.
 """
+import os
 import random
 
 import numpy as np
@@ -29,6 +37,7 @@ import torch
 
 from . import capi
 from .dist import GradAllReduce, broadcast_replica_state, shard_range, world
+from .nn import _PREC
 
 
 class TrainHooks:
@@ -59,7 +68,80 @@ def lr_schedule(epoch):
     return float(np.clip(1e-3 * (1 - (epoch - 8000) / 1000.), a_min=5e-4, a_max=1e-3))
 
 
-def run_training(model, datas, Bs, epochs=None, log=print, inner_batch=10000, steps_per_epoch=6, seed=0, hooks=None):
+class _PassGraph:
+    """One pass (<= 6 steps) over a batch of E environments as a replayable CUDA graph."""
+
+    def __init__(self, model, table, E, rows, bounds, rank, ws):
+        import torch.distributed as dist
+        net, opt = model.network, model.optimizer
+        fp = net.flat()
+        dev = fp.device
+        d = model.dim
+        self.fp, self.opt, self.E, self.steps, self.ws = fp, opt, E, len(bounds), ws
+        self.perm = torch.zeros(E, rows, dtype=torch.int32, device=dev)
+        self.off = torch.zeros(E, 1, dtype=torch.int32, device=dev)
+        self.off_host = torch.zeros(E, 1, dtype=torch.int32).pin_memory()
+        self.B = torch.zeros(E, d, 128, dtype=torch.float32, device=dev)
+        # per-step {alpha, beta * w, gamma}, per-step loss correction {beta c, c}, then {lr, step count}
+        n_cfg = 5 * self.steps + 2
+        self.cfg = torch.zeros(n_cfg, dtype=torch.float32, device=dev)
+        self.cfg_host = torch.zeros(n_cfg, dtype=torch.float32).pin_memory()
+        self.sched = self.cfg[:3 * self.steps].view(self.steps, 3)
+        self.corr = self.cfg[3 * self.steps:5 * self.steps].view(self.steps, 2)
+        self.lr_step = self.cfg[5 * self.steps:]
+        self.losses = torch.zeros(self.steps, 2, dtype=torch.float32, device=dev)
+        self.bounds = bounds                                  # (lo, b, e, n_g) per step: rows lo+b .. lo+e of a permutation
+        self.index = [torch.zeros(E * (e - b), dtype=torch.int32, device=dev) for (lo, b, e, n_g) in bounds]
+        self.diff = torch.zeros(E * max(e - b for (lo, b, e, n_g) in bounds), dtype=torch.float32, device=dev)
+        prec = _PREC[net.precision]
+        budget = net.stash_budget
+
+        def body():
+            for ii, (lo, b, e, n_g) in enumerate(bounds):
+                n = e - b
+                w = n * ws / float(n_g)
+                for j in range(E):
+                    torch.add(self.perm[j, lo + b:lo + e], self.off[j], out=self.index[ii][j * n:(j + 1) * n])
+                fp.grad.zero_()
+                capi.loss_gather_sched(model.variant, fp.flat, self.B, table, self.index[ii], E, n, d, self.sched[ii],
+                                       fp.grad, self.diff[:E * n], fp.loss_slot, prec=prec, budget=budget)
+                if w != 1.0:
+                    fp.loss_slot[1:].mul_(w)
+                if ws > 1:
+                    dist.all_reduce(fp.gradbuf, op=dist.ReduceOp.SUM)
+                self.lr_step[1:].add_(1.0)
+                opt.step_sched(self.lr_step, grad_scale=1.0 / ws)
+                torch.sub(fp.loss_slot / ws if ws > 1 else fp.loss_slot, self.corr[ii], out=self.losses[ii])
+
+        # every buffer the body touches exists (the first pass ran launch by launch: workspace, NCCL); capture
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+            body()
+
+    def run(self, perms, offsets, B, alpha, beta, gamma, lr, b_term):
+        """Refreshes the device-side inputs, replays, returns the per-step [loss, loss_n] (one device read)."""
+        E, ws = self.E, self.ws
+        for j in range(E):
+            self.perm[j].copy_(perms[j])
+            self.off_host[j, 0] = int(offsets[j])
+        self.off.copy_(self.off_host, non_blocking=True)
+        self.B.copy_(B)
+        h = self.cfg_host
+        for ii, (lo, b, e, n_g) in enumerate(self.bounds):
+            w = (e - b) * ws / float(n_g)
+            h[3 * ii + 0], h[3 * ii + 1], h[3 * ii + 2] = alpha, beta * w, gamma
+            c = (ws - 1) * b_term / (E * n_g)
+            h[3 * self.steps + 2 * ii], h[3 * self.steps + 2 * ii + 1] = beta * c, c
+        h[5 * self.steps], h[5 * self.steps + 1] = lr, float(self.opt.step_count)
+        self.cfg.copy_(h, non_blocking=True)
+        self.graph.replay()
+        self.opt.step_count += self.steps
+        return self.losses.tolist()
+
+
+def run_training(model, datas, Bs, epochs=None, log=print, inner_batch=10000, steps_per_epoch=6, seed=0, hooks=None,
+                 graph=None):
     multi = model.variant == capi.LOSS_MULTI
     net, opt = model.network, model.optimizer
     fp = net.flat()
@@ -101,6 +183,18 @@ def run_training(model, datas, Bs, epochs=None, log=print, inner_batch=10000, st
     table = torch.cat([t.to(device=dev, dtype=torch.float32) for t in datas]).contiguous()
     single_order = None                          # single: the loader's cumulative in-place shuffle (S:61-64)
 
+    if graph is None:
+        graph = os.environ.get("PNTF_TRAIN_GRAPH", "1") != "0"
+    pass_graphs = {}                             # environments per batch -> _PassGraph (built after the first eager pass)
+    eager_passes = 0
+    bounds = []
+    for ii in range(steps):
+        lo, hi = ii * inner_batch, min((ii + 1) * inner_batch, rows)
+        b, e_ = shard_range(hi - lo, rank, ws)
+        bounds.append((lo, b, e_, hi - lo))
+    if any(e_ - b == 0 for (lo, b, e_, n_g) in bounds):
+        graph = False                            # a rank with an empty shard skips its kernels: launch by launch only
+
     beta, current_diff, step = 1.0, 1.0, -2000.0 / 4000.0
     snap = lambda: (fp.flat.clone(), opt.snapshot())
     current_state = snap()
@@ -137,6 +231,19 @@ def run_training(model, datas, Bs, epochs=None, log=print, inner_batch=10000, st
                 last_B = Bs[grp[0]]              # M:1069: self.B = B[0, :]
                 # 0.01 |B|^2 of the multi loss (M:947) enters every rank's loss_n once: taken out ws-1 times below
                 b_term = 0.01 * float((B.double() ** 2).sum().item()) if (multi and ws > 1) else 0.0
+                if graph and eager_passes >= 1:
+                    pg = pass_graphs.get(E)
+                    if pg is None:
+                        pg = pass_graphs[E] = _PassGraph(model, table, E, rows, bounds, rank, ws)
+                    lr_now = opt.param_groups[0]['lr']
+                    step_losses = pg.run(perms, [offs[e] for e in grp], B, alpha, beta, gamma, lr_now, b_term)
+                    for ii, lo_ in enumerate(step_losses):
+                        lt = torch.tensor(lo_, dtype=torch.float32, device=dev)
+                        totals += lt
+                        hooks.on_step({"epoch": epoch, "step": ii, "envs": list(grp), "alpha": alpha, "beta": beta,
+                                       "gamma": gamma, "lr": lr_now, "loss_out": lt, "index": None})
+                    continue
+                eager_passes += 1
                 for ii in range(steps):
                     lo, hi = ii * inner_batch, min((ii + 1) * inner_batch, rows)
                     n_g = hi - lo

@@ -162,7 +162,9 @@ def run_multi_train(seed=21, d=3, rows=12000, epochs=8):
     print(log)
     # draws per while-iteration: DataLoader order (n=2), idx0, idx1 (n=rows)
     assert all(p.numel() in (2, rows) for p in rec.perms)
-    env_orders = np.stack([p.numpy() for p in rec.perms if p.numel() == 2]).astype(np.uint8)
+    # torch's RandomSampler draws randperm(n) twice per pass: the order it yields, then one more for the
+    # (empty) remainder `[:num_samples % n]`; the environment order of a pass is the first of each pair
+    env_orders = np.stack([p.numpy() for p in rec.perms if p.numel() == 2]).astype(np.uint8)[::2]
     row_perms = np.stack([p.numpy()[:10000] for p in rec.perms if p.numel() == rows]).astype(np.uint16)
     steps = np.asarray(rec.steps, np.float64)
     fx = dict(seed=seed, d=d, rows=rows, epochs=epochs, env_orders=env_orders, row_perms=row_perms, steps=steps,

@@ -187,7 +187,7 @@ def test_rollback_restores_the_chosen_snapshot(capi, tmp_path):
 
     hooks = Hooks()
     logs = []
-    run_training(model, datas, Bs, epochs=5, log=logs.append, hooks=hooks)
+    run_training(model, datas, Bs, epochs=5, log=logs.append, hooks=hooks, graph=False)   # launch by launch: the wrapper sees every step
 
     def same(a, b):
         return all(torch.equal(x, y) for x, y in zip(a[:3], b[:3])) and a[3] == b[3]
@@ -351,3 +351,98 @@ def test_query_sharding_is_a_no_op_without_a_process_group(capi):
     assert torch.equal(n1, n2)
     for i in range(0, 100, 17):
         assert torch.equal(m.path(w1, n1, i, 3), m.path(w2, n2, i, 3))
+
+
+@pytest.mark.parametrize("prec", ["fp32", "tc"])
+def test_graph_replayed_passes_equal_the_launch_by_launch_loop(capi, prec):
+    """from the second pass on, Model.train's pass (index build, zero, loss + backward, AdamW, loss
+    accumulation, x steps) is one CUDA-graph replay with alpha / beta / gamma / lr / step count read from device memory
+    (pntf_loss_bwd_gather_sched, pntf_adamw_sched).  Same numbers as the launch-by-launch loop up to the order of the
+    gradient atomics."""
+    from pntf.model import Model_multi
+    from pntf.trainer import run_training
+    rows, d = 30000, 3
+    envs = [train_fixture_env(80 + i, rows, d) for i in range(2)]
+    datas = [torch.from_numpy(np.concatenate([p.astype(np.float16).astype(np.float32), s], 1)) for p, s, _ in envs]
+    Bs = [torch.from_numpy(b) for _, _, b in envs]
+    hists, finals = [], []
+    for graph in (False, True):
+        torch.manual_seed(5)
+        m = Model_multi("", "", d, 2, device=DEV)
+        m.init_network()
+        m.network.precision = prec
+
+        class Hooks:
+            def __init__(self):
+                self.gen = torch.Generator().manual_seed(3)
+                self.steps = []
+
+            def randperm(self, n):
+                return torch.randperm(n, generator=self.gen)
+
+            def rollback_index(self):
+                return 1
+
+            def on_step(self, rec):
+                self.steps.append((rec["epoch"], rec["step"], rec["alpha"], rec["beta"], rec["lr"],
+                                   [float(x) for x in rec["loss_out"].tolist()]))
+
+            def on_epoch(self, rec):
+                pass
+
+        hooks = Hooks()
+        hist = run_training(m, datas, Bs, epochs=5, log=lambda s: None, hooks=hooks, graph=graph)
+        hists.append((hist, hooks.steps, m.optimizer.step_count))
+        finals.append(m.network.flat().flat.clone())
+    (h0, s0, c0), (h1, s1, c1) = hists
+    assert c0 == c1 == 5 * 3 and len(s0) == len(s1) == 15
+    tol = 2e-4 if prec == "fp32" else 2e-2
+    for a, b in zip(s0, s1):
+        assert a[:3] == b[:3] and a[4] == b[4]
+        assert abs(a[3] - b[3]) <= tol * abs(a[3])
+        np.testing.assert_allclose(b[5], a[5], rtol=tol)
+    np.testing.assert_allclose([x[1] for x in h1], [x[1] for x in h0], rtol=tol)
+    rel = float((finals[1] - finals[0]).abs().max() / finals[0].abs().max())
+    assert rel < (5e-3 if prec == "fp32" else 5e-2), rel
+
+
+def test_rollback_inside_graph_replayed_training(capi):
+    """The same rollback rule when passes are CUDA-graph replays: the optimiser's step count lives in device memory the
+    host rewrites before every replay, so a restored snapshot (weights, moments, step count) is what the next replay
+    continues from."""
+    from pntf import trainer as T
+    from pntf.model import Model_multi
+    rows, d = 10000, 3
+    envs = [train_fixture_env(90 + i, rows, d) for i in range(2)]
+    datas = [torch.from_numpy(np.concatenate([p.astype(np.float16).astype(np.float32), s], 1)) for p, s, _ in envs]
+    Bs = [torch.from_numpy(b) for _, _, b in envs]
+    torch.manual_seed(2)
+    model = Model_multi("", "", d, 2, device=DEV)
+    model.init_network()
+    fp, opt = model.network.flat(), model.optimizer
+    states = []
+    orig_run = T._PassGraph.run
+
+    def run(self, *a, **kw):
+        c = len(states)
+        states.append((fp.flat.clone(), opt.exp_avg.clone(), opt.exp_avg_sq.clone(), opt.step_count))
+        out = orig_run(self, *a, **kw)
+        if c == 2:                      # third graph pass = epoch 4, first attempt (epoch 1 runs launch by launch)
+            out = [[50.0 * x for x in row] for row in out]
+        return out
+
+    class Hooks(T.TrainHooks):
+        def rollback_index(self):
+            return 3                    # ring at epoch 4 = [S0, S0, S1, S2]: the start of epoch 3
+
+    T._PassGraph.run = run
+    try:
+        logs = []
+        T.run_training(model, datas, Bs, epochs=5, log=logs.append, hooks=Hooks(0, DEV), graph=True)
+    finally:
+        T._PassGraph.run = orig_run
+    # graph passes: epoch 2, epoch 3, epoch 4 (spiked), epoch 4 again, epoch 5
+    assert len(states) == 5 and sum("RepeatEpoch" in line for line in logs) == 1
+    assert all(torch.equal(x, y) for x, y in zip(states[3][:3], states[1][:3])) and states[3][3] == states[1][3] == 2
+    assert not torch.equal(states[3][0], states[2][0])
+    assert states[4][3] == 3 and opt.step_count == 4
