@@ -194,9 +194,9 @@ class _ModelBase:
         w = waypoints[q, :n]
         return torch.cat([w[:, :dim], torch.flip(w[:, dim:], dims=[0])], dim=0)
 
-    def field_slice(self, Xsrc=None, limit=0.5, n=80):
-        """Headless version of Model.plot (S:1284-1329, M:1250-1293): evaluates TravelTimes, Speed and
-        Tau on an n x n slice and returns (X, Y, TT, V, TAU) as numpy arrays (no matplotlib)."""
+    def _slice_points(self, Xsrc, limit, n):
+        """(X, Y, XP): the multi model's slice (M:1250-1266): source (-0.25, -0.25, 0, ...), goal = the grid point in
+        the first two coordinates and 0 beyond them.  Model_single overrides it with the UR5 slice of S:1284-1303."""
         spacing = 2 * limit / n
         ax = np.arange(-limit, limit, spacing)
         X, Y = np.meshgrid(ax, ax)
@@ -205,9 +205,15 @@ class _ModelBase:
             src[0] = -0.25
             src[1] = -0.25
         XP = np.zeros((X.size, 2 * self.dim))
-        XP[:, :self.dim] = src                   # goal coordinates beyond the slice plane stay 0 (M:1263-1266)
+        XP[:, :self.dim] = src
         XP[:, self.dim + 0] = X.flatten()
         XP[:, self.dim + 1] = Y.flatten()
+        return X, Y, XP
+
+    def field_slice(self, Xsrc=None, limit=None, n=80):
+        """Headless version of Model.plot (S:1284-1329, M:1250-1293): evaluates TravelTimes, Speed and
+        Tau on an n x n slice and returns (X, Y, TT, V, TAU) as numpy arrays (no matplotlib)."""
+        X, Y, XP = self._slice_points(Xsrc, self.slice_limit if limit is None else limit, n)
         XP = torch.tensor(XP, dtype=torch.float32, device=self._dev())
         tt = self.TravelTimes(XP)
         ss = self.Speed(XP)
@@ -226,6 +232,24 @@ class Model_single(_ModelBase):
     """Model(ModelPath, DataPath, dim, device) of models/model_res_sigmoid.py:829-1329 (UR5, d=6)."""
     variant = capi.LOSS_SINGLE
     default_grad_mode = 'exact'      # S:1254-1255 uses autograd: the exact gradient
+    slice_limit = 2.0                # S:1286
+
+    def _slice_points(self, Xsrc, limit, n):
+        """S:1284-1303: a UR5 configuration (radians) scaled by 0.5 / pi as start AND goal, the goal's first two joints
+        swept over [-limit, limit)^2."""
+        spacing = 2 * limit / n
+        ax = np.arange(-limit, limit, spacing)
+        X, Y = np.meshgrid(ax, ax)
+        if Xsrc is None:
+            Xsrc = [-1.3, 0.4 - 0.5 * np.pi, 1.1, 0.5 - 0.5 * np.pi, -0.5, 0.7][:self.dim] + [0.0] * max(0, self.dim - 6)
+        scale = np.pi / 0.5
+        XP = np.zeros((X.size, 2 * self.dim))
+        XP[:, :self.dim] = Xsrc
+        XP[:, self.dim:] = Xsrc
+        XP = XP / scale
+        XP[:, self.dim + 0] = X.flatten()
+        XP[:, self.dim + 1] = Y.flatten()
+        return X, Y, XP
 
     def __init__(self, ModelPath, DataPath, dim, device='cpu'):
         self.Params = _default_params(ModelPath, DataPath, device, 10000)
@@ -308,6 +332,7 @@ class Model_multi(_ModelBase):
     """Model(ModelPath, DataPath, dim, length, device) of models/model_res_sigmoid_multi.py:857-1293."""
     variant = capi.LOSS_MULTI
     default_grad_mode = 'compat'     # M:1221 uses out_backgrad as shipped
+    slice_limit = 0.5                # M:1251
 
     def __init__(self, ModelPath, DataPath, dim, length, device='cpu'):
         self.Params = _default_params(ModelPath, DataPath, device, 2)

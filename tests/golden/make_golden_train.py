@@ -230,7 +230,8 @@ def run_plot_slices(seed=41):
     del PLOT_CALLS[:]
     model.plot(1, 0.5, 0.5)
     calls = list(PLOT_CALLS)
-    fx.update(single_B=Bs, single_V=calls[0][1][2], single_TT=calls[1][1][2], single_TAU=calls[2][1][2])
+    fx.update(single_B=Bs, single_X=calls[0][1][0], single_Y=calls[0][1][1], single_V=calls[0][1][2],
+              single_TT=calls[1][1][2], single_TAU=calls[2][1][2])
     return fx
 
 

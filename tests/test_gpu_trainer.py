@@ -240,6 +240,7 @@ def test_reference_checkpoint_to_inference_and_field_slices(capi, tmp_path):
         _load_params(ms.network, P)
         ms.network.precision = prec
         X, Y, TT, V, TAU = ms.field_slice()
+        np.testing.assert_array_equal(X, fx["single_X"])         # S:1286-1290: [-2, 2)^2 in steps of 0.05
         np.testing.assert_allclose(TAU, fx["single_TAU"], rtol=tol / 10 if prec == "tc" else tol, atol=1e-7)
         np.testing.assert_allclose(TT, fx["single_TT"], rtol=tol / 10 if prec == "tc" else tol, atol=1e-6)
         np.testing.assert_allclose(V, fx["single_V"], rtol=tol, atol=1e-6)
