@@ -622,6 +622,16 @@ def speed_sampling_metric(dev, cpu=True, N=1 << 20, levels=6):
            "distance_queries_per_s_unsorted_inputs": N / sec_unsorted,
            "brute_force_equivalent_pair_tests_per_s": N * float(t.shape[0]) / sec_kernel,
            "sampler_pairs_per_s": want / sec_sampler, "sampler_pairs": want, "band": [offset, margin]}
+    # arm branch (:153-218): forward kinematics of a synthetic six-joint chain, 6 box links x 26 vertices per
+    # configuration against the same mesh, minimum over the arm
+    from pntf import arm_sampling as AS
+    J = [("l%d" % i, (0.0, 0.02 * (i % 2), 0.12), (0.0, 1.5708 * (i % 2), 0.0), ((0, 0, 1), (0, 1, 0))[i % 2]) for i in range(6)]
+    chain = AS.SerialChain([{"name": n_, "type": "revolute", "xyz": x_, "rpy": r_, "axis": a_} for n_, x_, r_, a_ in J], device=dev)
+    verts = {n_: AS.box_link_vertices((-0.02, -0.02, 0.0), (0.02, 0.02, 0.12)) for n_, _, _, _ in J}
+    th = (torch.rand(1 << 16, 6, device=dev, generator=g) - 0.5) * 6.2831855
+    sec_arm = timed(lambda: AS.arm_obstacle_distance(th, chain, verts, mesh), reps=2)
+    res["arm_configurations_per_s"] = th.shape[0] / sec_arm
+    res["arm_vertex_queries_per_s"] = th.shape[0] * 5 * verts["l0"].shape[0] / sec_arm      # base and first link are skipped (:168)
     if cpu:
         from oracle import mesh_oracle as MO                                       # CPU leg only
         n = 256

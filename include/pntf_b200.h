@@ -159,6 +159,14 @@ int pntf_mesh_distance(const float* triangles, int64_t M, const float* points, i
                        float offset, float margin, float* speed, void* workspace, size_t workspace_bytes,
                        void* stream);
 
+/* Run-to-run reproducible gradients (tensor-core mode).  By default the weight-gradient and bias-gradient partial sums
+ * of different CTAs / warps meet in fp32 atomics, whose order varies from run to run (last bits differ).  With on != 0
+ * (or PNTF_DETERMINISTIC=1 in the environment) pntf_loss_bwd* accumulates them as 64-bit fixed point (2^-24) in its
+ * workspace -- integer adds commute -- and converts once at the end: two calls on the same inputs return bit-identical
+ * grad_params.  The reference's autograd on CUDA gives no such guarantee either; this is for debugging and for
+ * replicas that must not drift.  Process-global. */
+int pntf_set_deterministic(int on);
+
 /* Measurement aid for bench.py: between begin and end every kernel (group) the library launches is
  * bracketed by CUDA events on its stream; end synchronises on them and returns, per kernel class
  * (0 pack, 1 forward, 2 reverse, 3 dW, 4 loss-finalize, 5 adamw, 6 plan, 7 tc-forward, 8 tc-reverse,

@@ -2,6 +2,7 @@
 // workspace carving, kernel launches.  No torch types, no allocation, no host synchronisation.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <cmath>
 #include <atomic>
@@ -62,6 +63,15 @@ int launch_check(const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(PNTF_ERR_CUDA, "launch %s: %s", what, cudaGetErrorString(e));
   return PNTF_OK;
+}
+
+static int g_deterministic = -1;
+bool deterministic_mode() {
+  if (g_deterministic < 0) {
+    const char* e = getenv("PNTF_DETERMINISTIC");
+    g_deterministic = (e != nullptr && atoi(e) != 0) ? 1 : 0;
+  }
+  return g_deterministic == 1;
 }
 
 int sm_count() {
@@ -230,6 +240,11 @@ extern "C" {
 int pntf_version(void) { return 100; }
 const char* pntf_last_error(void) { return g_err; }
 int64_t pntf_launch_count(void) { return g_launches.load(); }
+
+int pntf_set_deterministic(int on) {
+  g_deterministic = on ? 1 : 0;
+  return PNTF_OK;
+}
 
 int pntf_profile_begin(void) {
   g_prof_n = 0;

@@ -15,6 +15,7 @@ void prof_start(int cls, cudaStream_t s);
 void prof_stop(cudaStream_t s);
 int launch_check(const char* what);
 int sm_count();
+bool deterministic_mode();   // pntf_set_deterministic / PNTF_DETERMINISTIC
 int finalize_loss(int variant, const float* diff, int64_t n_total, const float* B, int E, int d, float beta,
                   float* loss_out, cudaStream_t s);   // beta is read from g_sched when that is set
 

@@ -28,6 +28,7 @@ struct TcDwArgs {
   // fused backward (tc_backward.cuh): wait for flags[tile * 16 + l] == epoch before reading Ybar_l of a tile
   const uint32_t* flags;
   uint32_t epoch;
+  long long* detw;          // deterministic mode: 64-bit fixed-point accumulators [PNTF_PARAM_COUNT] (tc_reverse.cuh: det_add)
 };
 
 // acquire side of the reverse sweep's flags (tc_reverse.cuh: flag_publish)
@@ -116,6 +117,7 @@ __device__ __forceinline__ void tc_dw_role(const TcDwArgs& a, const int cta) {
     const int m = tid & 127, half = tid >> 7;
     const uint32_t lane_base = tmem_base + (uint32_t((warp & 3) * 32) << 16);
     float* dst = a.grad + c_w[l] + size_t(h * 128 + m) * K;
+    long long* dstq = a.detw != nullptr ? a.detw + c_w[l] + size_t(h * 128 + m) * K : nullptr;
     const bool row_ok = (h * 128 + m) < M;
     const float sc = a.sched != nullptr ? __ldg(a.sched + 1) * a.inv_scale : a.out_scale;
     const int kc = K / 2;
@@ -124,7 +126,13 @@ __device__ __forceinline__ void tc_dw_role(const TcDwArgs& a, const int cta) {
       tmem_ld<32>(lane_base + c0, v);
       if (row_ok) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) atomicAdd(dst + c0 + j, v[j] * sc);
+        for (int j = 0; j < 32; ++j) {
+          if (dstq != nullptr)
+            atomicAdd(reinterpret_cast<unsigned long long*>(dstq + c0 + j),
+                      static_cast<unsigned long long>(__float2ll_rn(v[j] * 16777216.0f)));
+          else
+            atomicAdd(dst + c0 + j, v[j] * sc);
+        }
       }
     }
   }

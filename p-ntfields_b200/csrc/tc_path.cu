@@ -103,6 +103,30 @@ static int tc_tile_pairs(int d) {
   return d <= 3 ? TcCfg<3, 2>::P : TcCfg<6, 2>::P;
 }
 constexpr size_t kImgBytes = ((kFwdImgBytes + kRevImgBytes + 255) / 256) * 256;
+// deterministic mode: fixed-point accumulators detw[PNTF_PARAM_COUNT] and detb[kDetMaxCtas][kDetSlots] behind the images
+constexpr int kDetMaxCtas = 160;
+constexpr size_t kDetWBytes = ((size_t(PNTF_PARAM_COUNT) * 8 + 255) / 256) * 256;
+constexpr size_t kDetBytes = kDetWBytes + ((size_t(kDetMaxCtas) * kDetSlots * 8 + 255) / 256) * 256;
+constexpr size_t kHeadBytes = kImgBytes + kDetBytes;   // the stash begins here
+
+// grad[i] += (detw[i] + sum over CTAs of detb[cta][slot(i)]) * 2^-24 * scale: one thread per parameter, integer sums
+__global__ void det_finalize_kernel(const long long* __restrict__ detw, const long long* __restrict__ detb, int nctas,
+                                    float* __restrict__ grad, float out_scale, const float* __restrict__ sched,
+                                    float inv_scale) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= PNTF_PARAM_COUNT) return;
+  long long q = detw[i];
+  int slot = -1;
+  for (int l = 0; l <= 12; ++l)
+    if (i >= c_b[l] && i < c_b[l] + c_M[l]) slot = c_db[l] + (i - c_b[l]);
+  if (i >= c_w[13] && i < c_w[13] + 128) slot = kNumBiasSlots + (i - c_w[13]);
+  if (i == c_b[13]) slot = kNumBiasSlots + 128;
+  if (slot >= 0)
+    for (int c = 0; c < nctas; ++c) q += detb[size_t(c) * kDetSlots + slot];
+  if (q == 0) return;
+  const float sc = sched != nullptr ? sched[1] * inv_scale : out_scale;
+  grad[i] += float(double(q) * (1.0 / 16777216.0)) * sc;
+}
 
 size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes) {
   if (op != PNTF_OP_LOSS_BWD) return align256(kFwdImgBytes) + 512;
@@ -112,7 +136,7 @@ size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes) 
   size_t tiles = budget_bytes / stash_tile_bytes();
   if (tiles > ntiles) tiles = ntiles;
   if (tiles < 1) tiles = 1;
-  return kImgBytes + tiles * stash_tile_bytes() + 256;
+  return kHeadBytes + tiles * stash_tile_bytes() + 256;
 }
 
 static void tc_carve_stash(TcStash& st, uint8_t* base, size_t tiles) {
@@ -195,9 +219,16 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
   const int64_t n_total = int64_t(E) * N;
   uint8_t* fimg = ws;
   uint8_t* rimg = ws + kFwdImgBytes;
-  uint8_t* stash = ws + kImgBytes;
-  if (ws_bytes < kImgBytes + stash_tile_bytes()) return fail(PNTF_ERR_WORKSPACE, "workspace too small for one tile");
-  int64_t chunk_tiles = int64_t((ws_bytes - kImgBytes) / stash_tile_bytes());
+  uint8_t* stash = ws + kHeadBytes;
+  if (ws_bytes < kHeadBytes + stash_tile_bytes()) return fail(PNTF_ERR_WORKSPACE, "workspace too small for one tile");
+  int64_t chunk_tiles = int64_t((ws_bytes - kHeadBytes) / stash_tile_bytes());
+  const bool det = deterministic_mode() && sm_count() <= kDetMaxCtas;
+  long long* detw = det ? reinterpret_cast<long long*>(ws + kImgBytes) : nullptr;
+  long long* detb = det ? reinterpret_cast<long long*>(ws + kImgBytes + kDetWBytes) : nullptr;
+  if (det) {
+    cudaError_t e = cudaMemsetAsync(ws + kImgBytes, 0, kDetBytes, s);
+    if (e != cudaSuccess) return fail(PNTF_ERR_CUDA, "cudaMemsetAsync(det): %s", cudaGetErrorString(e));
+  }
   const int64_t ntiles_all = (n_total + C::P - 1) / C::P;
   if (chunk_tiles > ntiles_all) chunk_tiles = ntiles_all;
   if (int rc = tc_pack(params, fimg, rimg, s)) return rc;
@@ -228,6 +259,7 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     tc_carve_stash(a.st, stash, size_t(tiles));
     r.rimg = rimg; r.grad = grad_params; r.out_scale = out_scale;
     r.inv_scale = float(1.0 / (double(E) * double(N)) / double(kGradScale));
+    r.detb = detb;
     const int grid = int(tiles < sm_count() ? tiles : sm_count());
     a.trace = (t0 == 0) ? trace_begin() : nullptr;
     prof_start(KC_TC_FORWARD, s);
@@ -238,7 +270,7 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     if (int rc = launch_check("tc_forward(train)")) return rc;
     TcDwArgs dw{};
     dw.st = a.st; dw.units = units; dw.ntiles = tiles; dw.grad = grad_params; dw.out_scale = out_scale;
-    dw.sched = a.sched; dw.inv_scale = r.inv_scale;
+    dw.sched = a.sched; dw.inv_scale = r.inv_scale; dw.detw = detw;
     if (n_dw > 0) {
       // one launch: reverse sweep on the first CTAs, weight gradients trailing it on the last n_dw (tc_backward.cuh)
       uint32_t* flags = stash_flags(a.st, size_t(tiles));
@@ -268,6 +300,12 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     prof_stop(s);
     if (int rc = launch_check("tc_dw")) return rc;
   }
+  if (det) {
+    const float inv_scale = float(1.0 / (double(E) * double(N)) / double(kGradScale));
+    det_finalize_kernel<<<(PNTF_PARAM_COUNT + 255) / 256, 256, 0, s>>>(detw, detb, sm_count(), grad_params, out_scale,
+                                                                       g_sched, inv_scale);
+    if (int rc = launch_check("det_finalize")) return rc;
+  }
   return PNTF_OK;
 }
 
@@ -295,10 +333,10 @@ int tc_debug_adjoint_stats(const void* workspace, size_t workspace_bytes, int E,
                            unsigned long long* out, void* stream) {
   const size_t P = tc_tile_pairs(d);
   const size_t ntiles = (size_t(E) * size_t(N) + P - 1) / P;
-  if (workspace_bytes < kImgBytes + ntiles * stash_tile_bytes())
+  if (workspace_bytes < kHeadBytes + ntiles * stash_tile_bytes())
     return fail(PNTF_ERR_WORKSPACE, "the adjoint statistics need a call that fitted one chunk (%zu tiles)", ntiles);
   TcStash st{};
-  tc_carve_stash(st, const_cast<uint8_t*>(static_cast<const uint8_t*>(workspace)) + kImgBytes, ntiles);
+  tc_carve_stash(st, const_cast<uint8_t*>(static_cast<const uint8_t*>(workspace)) + kHeadBytes, ntiles);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   cudaError_t e = cudaMemsetAsync(out, 0, 4 * sizeof(unsigned long long), s);
   if (e != cudaSuccess) return fail(PNTF_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
@@ -416,7 +454,7 @@ int tc_loss(int with_grad, int variant, const float* params, const float* B, con
             float* grad_params, void* workspace, size_t workspace_bytes, void* stream) {
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (with_grad) {
-    if (int rc = tc_check_ws(workspace, workspace_bytes, kImgBytes + stash_tile_bytes())) return rc;
+    if (int rc = tc_check_ws(workspace, workspace_bytes, kHeadBytes + stash_tile_bytes())) return rc;
 #define PNTF_BWD(DD, OO) tc_loss_bwd<DD, OO>(variant, params, B, coords, speed, E, N, alpha, beta, gamma, diff, grad_params, \
                                             static_cast<uint8_t*>(workspace), workspace_bytes, s)
     int rc;

@@ -32,7 +32,17 @@ struct TcRevArgs {
   // global memory; the weight-gradient CTAs of the same launch wait on it.  nullptr: separate launches, no flags.
   uint32_t* flags;
   uint32_t epoch;
+  // Deterministic mode (pntf_set_deterministic): bias / output-layer gradient partial sums go to this CTA's row of
+  // detb[cta][kDetSlots] as 64-bit fixed point (integer adds commute: the result does not depend on the order in which
+  // warps and CTAs arrive), instead of fp32 adds in shared memory + fp32 atomics; tc_path.cu: det_finalize_kernel.
+  long long* detb;
 };
+
+constexpr int kDetSlots = 2432 + 129;          // kNumBiasSlots + dW13[128] + db13
+constexpr float kDetScale = 16777216.0f;        // 2^24 fractional bits
+__device__ __forceinline__ void det_add(long long* slot, float v) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(slot), static_cast<unsigned long long>(__float2ll_rn(v * kDetScale)));
+}
 
 constexpr int kFlagStride = 16;   // flag words per tile (13 layers used)
 
@@ -413,6 +423,7 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
     const uint32_t gt_addr = smem_u32(gt), x_addr = smem_u32(xbuf), sdb_addr = smem_u32(sdb);
     const float* prm = a.params;
     const float w13f = __ldg(prm + c_w[13] + p.lane);
+    long long* const detb = b.detb != nullptr ? b.detb + size_t(cta) * kDetSlots : nullptr;
     float dw13 = 0.f, unused = 0.f;
     uint32_t nar0 = 0, nar1 = 0, ny0 = 0, ny1 = 0, nsd0 = 0, nsd1 = 0;
     for (int64_t tile = cta; tile < ntiles; tile += ncta) {
@@ -481,7 +492,8 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
           }
           }
           gy[0] = yb;
-          atomicAdd(sdb + kNumBiasSlots + 128, yb);
+          if (detb != nullptr) det_add(detb + kNumBiasSlots + 128, yb);
+          else atomicAdd(sdb + kNumBiasSlots + 128, yb);
         }
 #pragma unroll
         for (int c = 0; c < C::STRIDE; ++c) g13s[C::pair_row(tid) + c] = gy[c];
@@ -495,7 +507,8 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
 #define PNTF_WAIT0() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); --tl; trace_evt(a.trace, tron, 1, tl, 0); PNTF_WAIT_SD0(); mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; trace_evt(a.trace, tron, 1, tl, 1); }
       // (operand-tile half 1 was last stored by step l+1, or for l = 11 by step 6 of the previous tile)
 #define PNTF_WAIT1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); if (l != 11 || tile != int64_t(cta)) PNTF_WAIT_SD1(); mbar_wait(&ctl.yb[1], ny1 & 1); ++ny1; }
-#define PNTF_DB(l, h, v) red_shared_add(sdb_addr + 4u * uint32_t(c_db[l] + (h) * 128 + p.lane), (v))
+#define PNTF_DB(l, h, v) { const float dbv = (v); if (detb != nullptr) det_add(detb + c_db[l] + (h) * 128 + p.lane, dbv); \
+                           else red_shared_add(sdb_addr + 4u * uint32_t(c_db[l] + (h) * 128 + p.lane), dbv); }
       // ---- generator (step 12 has no accumulator input; the operand tile was last stored by step 0 of the previous tile)
       if (tile != int64_t(cta)) PNTF_WAIT_SD0();
       { mbar_wait(&ctl.yb[0], ny0 & 1); ++ny0; trace_evt(a.trace, tron, 1, 12, 1); }
@@ -549,17 +562,20 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
       // g13s is rewritten by the next tile's seeds only after every thread has left step 12 of this tile:
       // the named barrier of the next tile comes after this tile's last publish of all threads
     }
-    atomicAdd(sdb + kNumBiasSlots + p.lane, dw13);
+    if (detb != nullptr) det_add(detb + kNumBiasSlots + p.lane, dw13);
+    else atomicAdd(sdb + kNumBiasSlots + p.lane, dw13);
     // ---- bias gradients (+ output layer weight gradient) of this CTA's tiles
     named_bar_sync(1, kEpiThreads);
     const float sc = a.sched != nullptr ? __ldg(a.sched + 1) * b.inv_scale : b.out_scale;
     float* gp = b.grad;
-    for (int l = 0; l <= 12; ++l) {
-      const int M = c_M[l];
-      for (int i = tid; i < M; i += kEpiThreads) atomicAdd(gp + c_b[l] + i, sdb[c_db[l] + i] * sc);
+    if (detb == nullptr) {
+      for (int l = 0; l <= 12; ++l) {
+        const int M = c_M[l];
+        for (int i = tid; i < M; i += kEpiThreads) atomicAdd(gp + c_b[l] + i, sdb[c_db[l] + i] * sc);
+      }
+      if (tid < 128) atomicAdd(gp + c_w[13] + tid, sdb[kNumBiasSlots + tid] * sc);
+      if (tid == 128) atomicAdd(gp + c_b[13], sdb[kNumBiasSlots + 128] * sc);
     }
-    if (tid < 128) atomicAdd(gp + c_w[13] + tid, sdb[kNumBiasSlots + tid] * sc);
-    if (tid == 128) atomicAdd(gp + c_b[13], sdb[kNumBiasSlots + 128] * sc);
   }
   tc_fence_before();
   __syncthreads();

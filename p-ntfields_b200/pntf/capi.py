@@ -21,7 +21,7 @@ OP_FORWARD, OP_LOSS_FWD, OP_LOSS_BWD, OP_PLAN, OP_FIELD = 0, 1, 2, 3, 4
 
 EXPORTS = ["pntf_version", "pntf_last_error", "pntf_param_offset", "pntf_workspace_bytes", "pntf_forward",
            "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_loss_fwd_gather", "pntf_loss_bwd_gather", "pntf_loss_bwd_gather_sched", "pntf_adamw", "pntf_adamw_sched", "pntf_plan", "pntf_plan_compact", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end",
-           "pntf_tc_selftest", "pntf_mesh_workspace_bytes", "pntf_mesh_distance", "pntf_debug_adjoint_stats"]
+           "pntf_tc_selftest", "pntf_mesh_workspace_bytes", "pntf_mesh_distance", "pntf_debug_adjoint_stats", "pntf_set_deterministic"]
 
 _lib = None
 
@@ -287,6 +287,11 @@ def adjoint_stats(E, N, d, budget=0, layer=-1):
     v = out.cpu().tolist()
     return {"inf_nan": v[0], "subnormal": v[1], "nonzero": v[2],
             "max_abs": struct.unpack("f", struct.pack("I", v[3] & 0xffffffff))[0]}
+
+
+def set_deterministic(on=True):
+    """Run-to-run bit-identical parameter gradients in tensor-core mode (64-bit fixed-point accumulation)."""
+    _check(lib().pntf_set_deterministic(1 if on else 0))
 
 
 def tc_selftest(W, X, C):

@@ -9,8 +9,9 @@ Mirrors dataprocessing/speed_sampling_gpu.py of the reference (same function nam
 
 The distance queries run in libpntf_b200.so (`pntf_mesh_distance`, hand-written CUDA) instead of the reference's
 third-party `bvh_distance_queries`; random numbers come from torch's CUDA generator exactly as in the reference, so
-a seeded run draws the same candidate stream.  The arm branch (:153-323) needs pytorch_kinematics and the robot's
-link meshes, which are not available: it is not mirrored.  There is no CPU fallback.
+a seeded run draws the same candidate stream.  The arm branch (:29-323) lives in pntf/arm_sampling.py (own serial-chain
+forward kinematics instead of pytorch_kinematics; the UR5's URDF / link meshes are not available offline, so
+`sample_speed` cannot read them and asks the caller for a chain and link meshes).  There is no CPU fallback.
 """
 import os
 
@@ -153,7 +154,9 @@ def sample_speed(path, numsamples, dim, task_name=None, device="cuda"):
         parts = out_path.split("/")
         task_name = parts[2] if len(parts) > 2 else ""
     if task_name == "arm":
-        raise NotImplementedError("arm sampling needs pytorch_kinematics and the robot link meshes (unavailable)")
+        raise NotImplementedError("arm datasets: call pntf.arm_sampling.arm_rand_sample_bound_points with a SerialChain "
+                                  "(SerialChain.from_urdf) and the links' collision-mesh vertices; the UR5 files the "
+                                  "reference reads from ./datasets/arm/UR5 are not part of this repository")
     file_name = os.path.splitext(os.path.basename(path))[0]
     input_file = os.path.join(out_path, file_name + "_scaled.off")
     offset, margin = band_for_task(task_name)

@@ -50,3 +50,33 @@ def test_off_reader_and_band(tmp_path):
     assert v.shape == (4, 3) and f.tolist() == [[0, 1, 2], [0, 1, 2], [0, 2, 3]]
     assert np.allclose(SS.band_for_task("gibson"), (0.5 / 120, 0.5 / 12))
     assert np.allclose(SS.band_for_task("test"), (0.01, 0.1))
+
+
+def test_arm_oracle_planar_two_link_closed_form():
+    """oracle/arm_oracle.py against a closed form: a planar two-link arm (links of length 1 along x, joints about z) and
+    a wall x = 3: the end point is (cos a + cos(a+b), sin a + sin(a+b)), the arm's distance to the wall is 3 - max x."""
+    from oracle import arm_oracle as AO
+    joints = [{"name": "l1", "type": "revolute", "xyz": (0, 0, 0), "rpy": (0, 0, 0), "axis": (0, 0, 1)},
+              {"name": "l2", "type": "revolute", "xyz": (1, 0, 0), "rpy": (0, 0, 0), "axis": (0, 0, 1)},
+              {"name": "tip", "type": "fixed", "xyz": (1, 0, 0), "rpy": (0, 0, 0), "axis": (1, 0, 0)}]
+    seg = np.stack([np.linspace(0, 1, 21), np.zeros(21), np.zeros(21)], axis=1)
+    verts = {"l1": seg, "l2": seg, "tip": np.zeros((1, 3))}
+    wall = np.array([[[3, -50, -50], [3, 50, -50], [3, 0, 80]]], np.float64)       # one huge triangle in the plane x = 3
+    rs = np.random.RandomState(0)
+    th = rs.uniform(-np.pi, np.pi, size=(40, 2))
+    fk = [AO.forward_kinematics(joints, t) for t in th]
+    tips = np.array([f[-1][1][:3, 3] for f in fk])
+    np.testing.assert_allclose(tips[:, 0], np.cos(th[:, 0]) + np.cos(th[:, 0] + th[:, 1]), atol=1e-12)
+    np.testing.assert_allclose(tips[:, 1], np.sin(th[:, 0]) + np.sin(th[:, 0] + th[:, 1]), atol=1e-12)
+    d = AO.arm_obstacle_distance(th, joints, verts, wall, first_link=1)
+    elbow_x = np.cos(th[:, 0])
+    want = 3.0 - np.maximum.reduce([np.zeros(40), elbow_x, tips[:, 0]])
+    np.testing.assert_allclose(d, want, atol=1e-9)
+    # rpy convention: yaw about z after pitch after roll (URDF fixed axes)
+    R = AO.rpy_matrix((0.3, -0.2, 0.7))
+    np.testing.assert_allclose(R @ R.T, np.eye(3), atol=1e-12)
+    np.testing.assert_allclose(AO.rpy_matrix((0, 0, np.pi / 2)) @ [1, 0, 0], [0, 1, 0], atol=1e-12)
+    # separating-axis oracle: a unit cube rotated 45 degrees about z touches / misses a neighbour as geometry says
+    T = np.eye(4); T[:3, :3] = AO.axis_angle((0, 0, 1), np.pi / 4); T[:3, 3] = (2.0, 0, 0)
+    assert AO.obb_overlaps_aabb(T, (0.5,) * 3, (-0.5,) * 3, (1.4, 1, 1), (0, -1, -1))          # corner reaches x = 2 - 0.707
+    assert not AO.obb_overlaps_aabb(T, (0.5,) * 3, (-0.5,) * 3, (1.2, 1, 1), (0, -1, -1))

@@ -116,3 +116,76 @@ def test_mesh_distance_rejects_bad_arguments(capi):
     assert L.pntf_mesh_distance(t.data_ptr(), 4, p.data_ptr(), 5, out.data_ptr(), 0.0, 0.0, None, None, 0, None) != 0
     assert b"workspace" in L.pntf_last_error()
     assert L.pntf_mesh_distance(t.data_ptr(), 0, p.data_ptr(), 5, out.data_ptr(), 0.0, 0.0, None, None, 0, None) != 0
+
+
+def _ur5_like_chain():
+    """A six-joint serial chain with UR5-like offsets (synthetic: the UR5's URDF and meshes are not available)."""
+    J = [("shoulder_link", (0, 0, 0.089), (0, 0, 0), (0, 0, 1)), ("upper_arm_link", (0, 0.136, 0), (0, 1.5708, 0), (0, 1, 0)),
+         ("forearm_link", (0, -0.12, 0.425), (0, 0, 0), (0, 1, 0)), ("wrist_1_link", (0, 0, 0.392), (0, 1.5708, 0), (0, 1, 0)),
+         ("wrist_2_link", (0, 0.093, 0), (0, 0, 0), (0, 0, 1)), ("wrist_3_link", (0, 0, 0.095), (0, 0, 0), (0, 1, 0))]
+    return [{"name": n, "type": "revolute", "xyz": xyz, "rpy": rpy, "axis": ax} for n, xyz, rpy, ax in J]
+
+
+def _urdf_of(joints):
+    links = ["base_link"] + [j["name"] for j in joints]
+    s = ["<robot name='synthetic'>"] + ["<link name='%s'/>" % l for l in links]
+    for parent, j in zip(links, joints):
+        s.append("<joint name='j_%s' type='%s'><parent link='%s'/><child link='%s'/><origin xyz='%s' rpy='%s'/>"
+                 "<axis xyz='%s'/></joint>" % (j["name"], j["type"], parent, j["name"], " ".join(map(str, j["xyz"])),
+                                               " ".join(map(str, j["rpy"])), " ".join(map(str, j["axis"]))))
+    return "\n".join(s + ["</robot>"])
+
+
+def test_arm_branch_fk_distance_and_obb_vs_oracle(capi):
+    """Arm branch of the sampler (dataprocessing/speed_sampling_gpu.py:76-218): forward kinematics of a serial chain
+    (built from URDF text), link vertices moved into the world, distance of the whole arm to the obstacle mesh with
+    pntf_mesh_distance, and the OBB pre-filter -- against oracle/arm_oracle.py (numpy float64)."""
+    from oracle import arm_oracle as AO
+    from pntf import arm_sampling as AS
+    joints = _ur5_like_chain()
+    chain = AS.SerialChain.from_urdf(_urdf_of(joints), "wrist_3_link", device=DEV)
+    assert chain.n_dof == 6 and chain.base_link == "base_link"
+    rs = np.random.RandomState(4)
+    th = rs.uniform(-np.pi, np.pi, size=(64, 6)).astype(np.float32)
+    tg = chain.forward_kinematics(torch.from_numpy(th).to(DEV))
+    assert list(tg.keys()) == ["base_link"] + [j["name"] for j in joints]
+    for i in (0, 17, 63):
+        for (name, T) in AO.forward_kinematics(joints, th[i])[1:]:
+            np.testing.assert_allclose(tg[name][i].cpu().numpy(), T, atol=2e-6)
+    boxes = {j["name"]: ((0.05, 0.05, 0.3), (-0.05, -0.05, 0.0)) for j in joints}
+    verts = {n: AS.box_link_vertices(lo, hi, n=3) for n, (hi, lo) in boxes.items()}
+    lo_o, hi_o = np.array([0.25, -0.3, 0.0]), np.array([0.6, 0.3, 0.5])
+    tri = MO.box_mesh(lo_o, hi_o).astype(np.float32)
+    d = AS.arm_obstacle_distance(torch.from_numpy(th).to(DEV), chain, verts, torch.from_numpy(tri).to(DEV).unsqueeze(0))
+    want = AO.arm_obstacle_distance(th, joints, verts, tri, first_link=2)
+    np.testing.assert_allclose(d.cpu().numpy(), want, atol=3e-6)
+    assert want.min() < 0.02 < want.max()
+    # OBB filter: the reference reports the LAST link's box only (:149); exact SAT oracle on that box
+    link_boxes = [np.array(boxes[j["name"]][0] + boxes[j["name"]][1], np.float32) for j in joints[2:]]
+    obs_box = np.concatenate([hi_o, lo_o]).astype(np.float32)
+    margin = 0.04
+    got = AS.arm_obstacle_obb(torch.from_numpy(th).to(DEV), chain, link_boxes, obs_box, margin).cpu().numpy()
+    last = joints[-1]["name"]
+    hi_b, lo_b = np.array(boxes[last][0]) + margin, np.array(boxes[last][1]) - margin
+    for i in range(64):
+        T = dict(AO.forward_kinematics(joints, th[i]))[last]
+        assert got[i] == AO.obb_overlaps_aabb(T, hi_b, lo_b, hi_o, lo_o), i
+    assert got.any() and not got.all()
+
+
+def test_arm_sampler_band_and_layout(capi):
+    from pntf import arm_sampling as AS
+    joints = _ur5_like_chain()
+    chain = AS.SerialChain(joints, device=DEV)
+    verts = {j["name"]: AS.box_link_vertices((-0.05, -0.05, 0.0), (0.05, 0.05, 0.3)) for j in joints}
+    lo_o, hi_o = np.array([0.25, -0.3, 0.0]), np.array([0.6, 0.3, 0.5])
+    v, f = MO.box_mesh(lo_o, hi_o).reshape(-1, 3), np.arange(36).reshape(12, 3)
+    torch.manual_seed(0)
+    margin = 0.5 / 12
+    pts, speed = AS.arm_rand_sample_bound_points(300, 6, v, f, margin / 10, margin, chain, verts, device=DEV)
+    assert pts.shape == (300, 12) and speed.shape == (300, 2)
+    assert np.abs(pts).max() <= 0.5 and speed.min() >= 0.1 - 1e-6 and speed.max() <= 1.0 + 1e-6
+    d0 = AS.arm_obstacle_distance(torch.from_numpy(pts[:, :6]).to(DEV) * (np.pi / 0.5), chain, verts,
+                                  torch.from_numpy(MO.box_mesh(lo_o, hi_o).astype(np.float32)).to(DEV).unsqueeze(0))
+    assert float(d0.min()) >= margin / 10 - 1e-6 and float(d0.max()) <= margin + 1e-6      # starts lie in the band (:260)
+    np.testing.assert_allclose(speed[:, 0], np.clip(d0.cpu().numpy(), margin / 10, margin) / margin, rtol=1e-5)

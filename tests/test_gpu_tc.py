@@ -286,3 +286,36 @@ def test_tc_value_only_rows_multi_env(capi, d, E, N):
     tt = capi.field(capi.FIELD_TRAVEL_TIME, flat, cu(Bw), cu(c), E, N, d, prec=capi.PREC_TC)
     want = np.linalg.norm(c[:, d:] - c[:, :d], axis=1) / t0.cpu().numpy()
     assert np.abs(tt.cpu().numpy().reshape(-1) - want).max() / np.abs(want).max() < 1e-5
+
+
+@pytest.mark.parametrize("d,E,N,budget_tiles", [(3, 2, 4000, 0), (3, 1, 6000, 150), (6, 1, 1500, 0)])
+def test_deterministic_mode_gives_bit_identical_gradients(capi, d, E, N, budget_tiles):
+    """pntf_set_deterministic: the weight- and bias-gradient partial sums of different CTAs / warps are accumulated as
+    64-bit fixed point (integer adds commute), so two calls on the same inputs return bit-identical gradients -- also
+    when the batch is processed in several stash chunks -- and they agree with the default (fp32 atomics) path."""
+    from pntf import synth
+    P = O.init_params(3)
+    flat = flat_from(P)
+    B = synth.sample_B(d, DEV, seed=1, E=E).contiguous()
+    c, s = synth.sample_pairs(E * N, d, DEV, seed=5)
+    variant = capi.LOSS_MULTI if d == 3 else capi.LOSS_SINGLE
+    budget = 0
+    if budget_tiles:
+        per_tile = (capi.workspace_bytes(capi.OP_LOSS_BWD, 1, 12 * 1000, d, capi.PREC_TC) -
+                    capi.workspace_bytes(capi.OP_LOSS_BWD, 1, 12 * 500, d, capi.PREC_TC)) // 500
+        budget = budget_tiles * per_tile
+    runs = []
+    try:
+        for mode in (True, True, False):
+            capi.set_deterministic(mode)
+            g = torch.zeros_like(flat)
+            lo, _ = capi.loss(variant, flat, B, c, s, E, N, d, 0.7, 1.3, 1e-3, grad_out=g, prec=capi.PREC_TC, budget=budget)
+            torch.cuda.synchronize()
+            runs.append((g.clone(), lo.clone()))
+    finally:
+        capi.set_deterministic(False)
+    assert torch.equal(runs[0][0], runs[1][0]) and torch.equal(runs[0][1], runs[1][1])
+    assert float(runs[0][0].abs().max()) > 0
+    ref = runs[2][0]
+    assert float((runs[0][0] - ref).abs().max() / ref.abs().max()) < 1e-5
+    assert float(runs[0][0][82432:115328].abs().max()) == 0.0      # encoder1.0.* (never executed) stays untouched

@@ -272,14 +272,15 @@ def test_autograd_and_optimizer_semantics_of_the_drop_in(capi):
     loss.backward()
     g1 = fp.grad.clone()
     assert float(g1.abs().max()) > 0
+    tiny = 2e-6 * float(g1.abs().max())       # the gradient atomics' order differs between calls: last bits
     w = named["generator.1.weight"]
     assert w.grad is not None and w.grad.data_ptr() == fp.grad_views["generator.1.weight"].data_ptr()
     assert named["encoder1.0.weight"].grad is None and named["encoder1.0.bias"].grad is None
     # a second call accumulates, with the incoming scale
     loss2, _, _ = m.Loss(pts, spd, B, 2.0, 1e-3)
     (3.0 * loss2).backward()
-    torch.testing.assert_close(fp.grad, 4.0 * g1, rtol=2e-5, atol=1e-9)
-    torch.testing.assert_close(w.grad, 4.0 * g1[fp.offsets["generator.1.weight"]:][:w.numel()].view_as(w), rtol=2e-5, atol=1e-9)
+    torch.testing.assert_close(fp.grad, 4.0 * g1, rtol=2e-5, atol=4 * tiny)
+    torch.testing.assert_close(w.grad, 4.0 * g1[fp.offsets["generator.1.weight"]:][:w.numel()].view_as(w), rtol=2e-5, atol=4 * tiny)
     # clipping p.grad in place is what the optimiser applies
     torch.nn.utils.clip_grad_norm_([p for k, p in named.items() if p.grad is not None], 1e-3)
     assert abs(float(torch.linalg.norm(fp.grad)) - 1e-3) < 1e-5
@@ -288,7 +289,7 @@ def test_autograd_and_optimizer_semantics_of_the_drop_in(capi):
     # gradient through loss_n alone = gradient through loss / beta
     _, ln, _ = m.Loss(pts, spd, B, 2.0, 1e-3)
     ln.backward()
-    torch.testing.assert_close(fp.grad, g1 / 2.0, rtol=2e-5, atol=1e-9)
+    torch.testing.assert_close(fp.grad, g1 / 2.0, rtol=2e-5, atol=tiny)
     m.optimizer.zero_grad()
     # no_grad: same numbers, no gradient work
     with torch.no_grad():
