@@ -64,6 +64,7 @@ struct TcFwdArgs {
   int32_t* nsteps;          // [Q]
   int* tile_counter;        // zeroed by the host: path queries are handed out to free tile slots dynamically
   int fill_tail;            // 1: rows after a query's last step repeat the final position (pntf_plan); 0: left untouched
+  const int32_t* order;     // hand-out order of the queries (longest start-goal distance first), or null: input order
 };
 
 // debug time stamps: slot layout [role][layer][event]
@@ -752,7 +753,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
               for (int i = 0; i < 2 * D; ++i) t0.x[tid][i] = 0.f;
               break;
             }
-            const int64_t pair = a.pair_begin + q;
+            const int64_t pair = a.pair_begin + (a.order != nullptr ? int64_t(__ldg(a.order + q)) : q);
             float* w = a.waypoints + pair * wstride;
             float d2 = 0.f;
 #pragma unroll

@@ -129,6 +129,7 @@ __global__ void det_finalize_kernel(const long long* __restrict__ detw, const lo
 }
 
 size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes) {
+  if (op == PNTF_OP_PLAN) return align256(kFwdImgBytes) + 2048 + align256(size_t(N) * 4) + 256;   // + counters + hand-out order
   if (op != PNTF_OP_LOSS_BWD) return align256(kFwdImgBytes) + 512;
   const size_t P = tc_tile_pairs(d);
   const size_t ntiles = (size_t(E) * size_t(N) + P - 1) / P;
@@ -413,6 +414,44 @@ int tc_field(int kind, int grad_flavour, const float* params, const float* B, co
   return tc_launch_forward<6, 1, false, TC_TAIL_FIELD>(a, s);
 }
 
+// ---- hand-out order of the path queries: longest start-goal distance first.  A query needs about |x1 - x0| / (2 eta)
+// steps and a pass over a tile takes the same time however many of its slots are live, so the run ends with a tail of
+// nearly empty passes as long as the longest query; starting the long queries first (longest-processing-time-first
+// scheduling) leaves only short ones for the tail.  Counting sort by quantised distance, 256 buckets; the order inside
+// a bucket is arbitrary, which cannot change results (rows of a tile are independent; tests/test_gpu_fullsize.py).
+constexpr int kPlanBuckets = 256;
+template <int D>
+__device__ __forceinline__ int plan_bucket(const float* sg, int64_t q) {
+  float d2 = 0.f;
+#pragma unroll
+  for (int i = 0; i < D; ++i) { const float v = __ldg(sg + q * 2 * D + D + i) - __ldg(sg + q * 2 * D + i); d2 = fmaf(v, v, d2); }
+  const int b = int(sqrtf(d2) * (float(kPlanBuckets) / 2.5f));     // the unit box has diameter sqrt(6) < 2.5
+  return kPlanBuckets - 1 - (b < 0 ? 0 : (b > kPlanBuckets - 1 ? kPlanBuckets - 1 : b));   // descending distance
+}
+template <int D>
+__global__ void plan_hist_kernel(const float* __restrict__ sg, int64_t Q, int* __restrict__ hist) {
+  const int64_t q = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (q < Q) atomicAdd(hist + plan_bucket<D>(sg, q), 1);
+}
+__global__ void plan_scan_kernel(int* hist) {      // exclusive scan of 256 counters in place (one block of 256 threads)
+  __shared__ int s[kPlanBuckets];
+  const int t = threadIdx.x;
+  s[t] = hist[t];
+  __syncthreads();
+  for (int o = 1; o < kPlanBuckets; o <<= 1) {
+    const int v = t >= o ? s[t - o] : 0;
+    __syncthreads();
+    s[t] += v;
+    __syncthreads();
+  }
+  hist[t] = t ? s[t - 1] : 0;
+}
+template <int D>
+__global__ void plan_scatter_kernel(const float* __restrict__ sg, int64_t Q, int* __restrict__ cursor, int32_t* __restrict__ order) {
+  const int64_t q = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (q < Q) order[atomicAdd(cursor + plan_bucket<D>(sg, q), 1)] = int32_t(q);
+}
+
 // Batched path integration on the tensor cores: first-order forward per step, queries handed out per tile.
 int tc_plan(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta, float thr,
             int max_iter, int grad_flavour, int fill_tail, float* waypoints, int32_t* nsteps, void* workspace,
@@ -421,10 +460,23 @@ int tc_plan(const float* params, const float* B, const float* start_goal, int64_
   if (int rc = tc_check_ws(workspace, workspace_bytes, align256(kFwdImgBytes) + 256)) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   uint8_t* img = static_cast<uint8_t*>(workspace);
-  int* counter = reinterpret_cast<int*>(img + align256(kFwdImgBytes));
+  int* counter = reinterpret_cast<int*>(img + align256(kFwdImgBytes));        // [0]: query counter, [64 .. 320): buckets
   if (int rc = tc_pack(params, img, nullptr, s)) return rc;
-  cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), s);
+  cudaError_t e = cudaMemsetAsync(counter, 0, 2048, s);
   if (e != cudaSuccess) return fail(PNTF_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
+  // hand-out order (needs 4 Q bytes of workspace behind the counters; dense queries only)
+  int32_t* order = nullptr;
+  const size_t order_off = align256(kFwdImgBytes) + 2048;
+  static const bool order_off_env = [] { const char* e = getenv("PNTF_PLAN_ORDER"); return e != nullptr && atoi(e) == 0; }();
+  if (!order_off_env && g_gather.index == nullptr && Q < (int64_t(1) << 31) && workspace_bytes >= order_off + size_t(Q) * 4) {
+    order = reinterpret_cast<int32_t*>(img + order_off);
+    int* hist = counter + 64;
+    const unsigned nb = unsigned((Q + 255) / 256);
+    if (d == 3) plan_hist_kernel<3><<<nb, 256, 0, s>>>(start_goal, Q, hist); else plan_hist_kernel<6><<<nb, 256, 0, s>>>(start_goal, Q, hist);
+    plan_scan_kernel<<<1, kPlanBuckets, 0, s>>>(hist);
+    if (d == 3) plan_scatter_kernel<3><<<nb, 256, 0, s>>>(start_goal, Q, hist, order); else plan_scatter_kernel<6><<<nb, 256, 0, s>>>(start_goal, Q, hist, order);
+    if (int rc = launch_check("plan_order")) return rc;
+  }
   TcFwdArgs a{};
   a.params = params; a.wimg = img; a.B = B; a.coords = start_goal;
   apply_gather(a, d);
@@ -432,6 +484,7 @@ int tc_plan(const float* params, const float* B, const float* start_goal, int64_
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
   a.eta = eta; a.thr = thr; a.max_iter = max_iter; a.waypoints = waypoints; a.nsteps = nsteps; a.tile_counter = counter;
   a.fill_tail = fill_tail;
+  a.order = order;
   const int64_t P = (d == 3) ? TcCfg<3, 1>::P : TcCfg<6, 1>::P;
   const int64_t ntiles = (Q + P - 1) / P;
   const int grid = int(ntiles < sm_count() ? ntiles : sm_count());
