@@ -35,6 +35,12 @@ inline void apply_gather(A& a, int d) {
   a.cstride = g_gather.index ? g_gather.row_stride : 2 * d;
   a.sstride = g_gather.index ? g_gather.row_stride : 2;
 }
+// tensor-core forward: dense, 16-byte aligned coordinates are streamed into shared memory by bulk copies
+template <class A>
+inline void apply_coords_bulk(A& a) {
+  a.coords_bulk = (a.index == nullptr && (reinterpret_cast<uintptr_t>(a.coords) & 15) == 0) ? 1 : 0;
+}
+
 size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes);
 
 int tc_forward(int mode, int grad_flavour, const float* params, const float* B, const float* coords, int E, int64_t N,

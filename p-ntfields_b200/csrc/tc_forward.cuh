@@ -65,6 +65,7 @@ struct TcFwdArgs {
   int* tile_counter;        // zeroed by the host: path queries are handed out to free tile slots dynamically
   int fill_tail;            // 1: rows after a query's last step repeat the final position (pntf_plan); 0: left untouched
   const int32_t* order;     // hand-out order of the queries (longest start-goal distance first), or null: input order
+  int coords_bulk;          // 1: dense, 16-byte aligned coordinates -> a tile's P x 2D floats arrive by one bulk copy (TMA)
 };
 
 // debug time stamps: slot layout [role][layer][event]
@@ -318,6 +319,7 @@ struct TcCtl {
   uint64_t go;                  // completes once per announcement
   volatile int more;            // 1 = another pass follows, 0 = the CTA is done
   uint32_t ready;               // PNTF_HELPER_POLL: weight stages landed so far (written by the helper thread)
+  uint64_t cbar[2];             // coordinates of the tile in ts[i] have landed (one completion per load_tile call)
 };
 
 // all epilogue threads (converged warps): half h of the next operand tile (and its TMEM pre-loads) is complete.
@@ -442,6 +444,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
   constexpr int S = kFwdRing;
   constexpr int CGP = C::CGP, P = C::P;
   constexpr bool PLAN = (TAIL == TC_TAIL_PLAN);
+  // who fetches a tile's coordinates: the MMA warp with one bulk copy per tile (COORD_TMA), or -- value-only rows, 64 pairs
+  // per tile, where the extra work in the MMA warp measured 12 % slower -- the tail threads with per-thread loads
+  constexpr bool COORD_TMA = !PLAN && ORDER != 0;
   static_assert(!PLAN || (ORDER == 1 && !TRAIN), "path integration runs the first-order forward");
   constexpr int ACC_A = 0, ACC_B = 256;       // TMEM accumulator regions (columns)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -449,7 +454,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
   uint8_t* act = smem;                        // two operand-tile buffers: X_l in buffer l & 1
   uint8_t* ring = smem + 2 * kTileBytes;
   __shared__ TcCtl<S> ctl;
-  __shared__ TcTile<C> ts[2];
+  __shared__ __align__(16) TcTile<C> ts[2];
   __shared__ float y13s[2][kRows];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane_id = tid & 31;
@@ -462,6 +467,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     for (int i = 0; i < 4; ++i) mbar_init(&ctl.sd[i >> 1][i & 1], 1);
     for (int i = 0; i < 4; ++i) mbar_init(&ctl.xio[i >> 1][i & 1], 1);
     mbar_init(&ctl.go, 1);
+    mbar_init(&ctl.cbar[0], 1);
+    mbar_init(&ctl.cbar[1], 1);
     ctl.ready = 0;
     fence_barrier_init();
   }
@@ -495,7 +502,51 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     // ------------------------------------------------------------- MMA issuer (converged warp, elected lane issues)
     uint32_t it = 0, nx0 = 0, nx1 = 0, npass = 0;
     const uint32_t ring_addr = smem_u32(ring), act_addr = smem_u32(act);
-    for (int64_t tile = blockIdx.x; PLAN || tile < ntiles; tile += gridDim.x) {
+    // Coordinates of tile `tile` into ts[i] (north_star: "streams coordinate pairs into shared memory with TMA").  Dense
+    // input (coords_bulk) and a full tile: the tile's P x 2D floats are contiguous in global memory and in ts[i].x, ONE
+    // bulk copy (cp.async.bulk) fetches them; ragged last tile / gathered batches (pntf_loss_*_gather): per-lane loads.
+    // cbar[i] completes once per call; the epilogue threads wait on it before the tile's Fourier features.  This warp
+    // does it because its register budget is free (the same fetch in the epilogue warps made ptxas spill there) and
+    // because it knows when ts[i] is free: once it has seen the first operand half of tile k + 1, every epilogue warp
+    // has left tile k's tail, the last reader of ts[k & 1].
+    static_assert(sizeof(TcTile<C>) % 16 == 0 && (P * 2 * D * sizeof(float)) % 16 == 0, "bulk copies move 16-byte units");
+    auto load_coords = [&](int64_t tile, int i) {
+      TcTile<C>& t = ts[i];
+      const int64_t first = a.pair_begin + tile * P;
+      const int64_t end = (a.pair_begin + a.pair_count < a.n_total) ? a.pair_begin + a.pair_count : a.n_total;
+      const bool bulk = a.coords_bulk != 0 && tile < ntiles && first + P <= end;
+#pragma unroll
+      for (int base = 0; base < P; base += 32) {
+        const int k = base + lane_id;
+        if (k < P) {
+          const int64_t pair = first + k;
+          const bool valid = tile < ntiles && pair < end;
+          t.valid[k] = valid;
+          t.env[k] = valid ? int(pair / a.n_per_env) : 0;
+          if (!bulk) {
+#pragma unroll
+            for (int c = 0; c < 2 * D; ++c) t.x[k][c] = valid ? __ldg(a.coords + src_row(a, pair) * a.cstride + c) : 0.f;
+          }
+        }
+      }
+      __syncwarp();
+      if (lane_id == 0) {
+        if (bulk) {
+          fence_proxy_async();   // earlier generic-proxy reads of ts[i].x are ordered before the async-proxy write
+          mbar_arrive_expect_tx(&ctl.cbar[i], uint32_t(P * 2 * D * sizeof(float)));
+          bulk_g2s(&t.x[0][0], a.coords + first * 2 * D, uint32_t(P * 2 * D * sizeof(float)), &ctl.cbar[i]);
+        } else {
+          mbar_arrive(&ctl.cbar[i]);
+        }
+      }
+      __syncwarp();
+    };
+    if constexpr (COORD_TMA) {
+      load_coords(blockIdx.x, 0);
+      load_coords(int64_t(blockIdx.x) + gridDim.x, 1);
+    }
+    uint32_t ktile = 0;
+    for (int64_t tile = blockIdx.x; PLAN || tile < ntiles; tile += gridDim.x, ++ktile) {
       if constexpr (PLAN) {
         mbar_wait(&ctl.go, npass & 1);
         ++npass;
@@ -534,6 +585,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
               trace_evt(a.trace, lane_id == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x, 0, l, 2 + h);   // commit of half h issued
             }
           }
+        }
+        if constexpr (COORD_TMA) {
+          // layer 0 of tile k is issued: tile k - 1's tail is over, its coordinate buffer takes tile k + 1's pairs
+          if (l == 0 && ktile > 0) load_coords(tile + int64_t(gridDim.x), int((ktile + 1) & 1));
         }
       }
     }
@@ -601,10 +656,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     uint32_t nar0 = 0, nar1 = 0;
     const bool compat = a.compat != 0;
     // coordinates of the CTA's first two tiles (later tiles are fetched two tiles ahead by the tail threads)
-    // coordinates of the CTA's first two tiles (later tiles are fetched two tiles ahead by the tail threads).
-    // A bulk-copy (cp.async.bulk) variant of this fetch was built and measured in round 2: correct, but its extra live
-    // state made ptxas spill in 19 of the 22 instantiations of this kernel (96 registers at 608 threads) and cost the
-    // training forward 5 ms per 1 Mi pairs for 27 MB of traffic per step, so the per-thread loads stay.
+    // COORD_TMA: the coordinates of a tile (ts[k & 1]) are fetched by the MMA warp (load_coords above); cbar[k & 1]
+    // completes when they have landed.  Otherwise the tail threads fetch them two tiles ahead with per-thread loads.
+    uint32_t ntile = 0;      // tiles this CTA has started: tile k uses ts[k & 1], whose barrier is then in phase (k >> 1) & 1
     auto load_tile = [&](int64_t tile, TcTile<C>& t) {
       const int64_t pair = a.pair_begin + tile * P + tid;
       const bool valid = tile < ntiles && pair < a.pair_begin + a.pair_count && pair < a.n_total;
@@ -613,7 +667,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
 #pragma unroll
       for (int i = 0; i < 2 * D; ++i) t.x[tid][i] = valid ? __ldg(a.coords + src_row(a, pair) * a.cstride + i) : 0.f;
     };
-    if constexpr (!PLAN) {
+    if constexpr (!PLAN && !COORD_TMA) {
       if (tid < P) {
         load_tile(blockIdx.x, ts[0]);
         load_tile(int64_t(blockIdx.x) + gridDim.x, ts[1]);
@@ -641,6 +695,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
         PNTF_WAIT_SD1();
         PNTF_WAIT_SD1();
       }
+      if constexpr (COORD_TMA) { mbar_wait(&ctl.cbar[par], (ntile >> 1) & 1); ++ntile; }   // this tile's coordinates have landed
       fourier_tile<C>(a, ts[par], buf0);
       PNTF_PUB(0);
       PNTF_PUB(1);
@@ -903,9 +958,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
           }
           }
         }
-        // this buffer's next user is the tile after next: fetch its coordinates now (the barrier of the
-        // next tile orders these writes before its readers)
-        load_tile(tile + 2 * int64_t(gridDim.x), ts[par]);
+        // this buffer's next user is the tile after next: COORD_TMA -> the MMA warp refills it (load_coords); else fetch
+        // its coordinates now (the barrier of the next tile orders these writes before its readers)
+        if constexpr (!COORD_TMA) load_tile(tile + 2 * int64_t(gridDim.x), ts[par]);
       }
     }
 #undef PNTF_WAIT_ACC0

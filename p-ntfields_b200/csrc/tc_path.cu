@@ -255,6 +255,7 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     TcFwdArgs& a = r.f;
     a.params = params; a.wimg = fimg; a.B = B; a.coords = coords; a.speed = speed;
     apply_gather(a, D);
+    apply_coords_bulk(a);
     a.n_total = n_total; a.n_per_env = N; a.pair_begin = begin; a.pair_count = count;
     a.diff = diff; a.single_variant = (variant == PNTF_LOSS_SINGLE); a.alpha = alpha; a.gamma = gamma;
     tc_carve_stash(a.st, stash, size_t(tiles));
@@ -372,6 +373,7 @@ int tc_forward(int mode, int grad_flavour, const float* params, const float* B, 
   TcFwdArgs a{};
   a.params = params; a.wimg = img; a.B = B; a.coords = coords;
   apply_gather(a, d);
+  apply_coords_bulk(a);
   a.n_total = int64_t(E) * N; a.n_per_env = N; a.pair_begin = 0; a.pair_count = a.n_total;
   a.tau = tau; a.dtau = (mode >= PNTF_MODE_GRAD) ? dtau : nullptr; a.ltau = ltau;
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
@@ -397,6 +399,7 @@ int tc_field(int kind, int grad_flavour, const float* params, const float* B, co
   TcFwdArgs a{};
   a.params = params; a.wimg = img; a.B = B; a.coords = coords;
   apply_gather(a, d);
+  apply_coords_bulk(a);
   a.n_total = int64_t(E) * N; a.n_per_env = N; a.pair_begin = 0; a.pair_count = a.n_total;
   a.field = out; a.field_kind = kind; a.gamma = gamma;
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
@@ -480,6 +483,7 @@ int tc_plan(const float* params, const float* B, const float* start_goal, int64_
   TcFwdArgs a{};
   a.params = params; a.wimg = img; a.B = B; a.coords = start_goal;
   apply_gather(a, d);
+  apply_coords_bulk(a);
   a.n_total = Q; a.n_per_env = Q; a.pair_begin = 0; a.pair_count = Q;
   a.compat = (grad_flavour == PNTF_GRAD_COMPAT);
   a.eta = eta; a.thr = thr; a.max_iter = max_iter; a.waypoints = waypoints; a.nsteps = nsteps; a.tile_counter = counter;
@@ -523,6 +527,7 @@ int tc_loss(int with_grad, int variant, const float* params, const float* B, con
   TcFwdArgs a{};
   a.params = params; a.wimg = img; a.B = B; a.coords = coords; a.speed = speed;
   apply_gather(a, d);
+  apply_coords_bulk(a);
   a.n_total = int64_t(E) * N; a.n_per_env = N; a.pair_begin = 0; a.pair_count = a.n_total;
   a.diff = diff; a.single_variant = (variant == PNTF_LOSS_SINGLE); a.alpha = alpha; a.gamma = gamma;
   int rc;
