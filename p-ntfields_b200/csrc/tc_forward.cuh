@@ -684,6 +684,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
 #define PNTF_WAIT_ACC0() { mbar_wait(&ctl.ar[0], nar0 & 1); ++nar0; tc_fence_after(); ++tl; trace_evt(a.trace, tron, trole, tl, 0); }
 #define PNTF_WAIT_ACC1() { mbar_wait(&ctl.ar[1], nar1 & 1); ++nar1; tc_fence_after(); trace_evt(a.trace, tron, trole, tl, 2); }
 #define PNTF_PUB(h) { epi_publish(&ctl.xr[h]); trace_evt(a.trace, tron, trole, tl < 0 ? 15 : tl, 1 + 2 * (h)); }
+    // Bias of the epilogue that follows (loaded one epilogue earlier) and the load for the one after it.  The barrier
+    // waits are volatile asm with a memory clobber, so a load written after them cannot be hoisted: issued here, before
+    // the waits, its L2 latency (a tile reads 10 KB of biases, more than L1 keeps next to 213 KB of shared memory)
+    // overlaps the wait and the epilogue instead of preceding every one of the 20 epilogues of a tile.
+#define PNTF_BIAS(next_ptr) { bcur = bnext; bnext = __ldg(next_ptr); }
+    float bcur = 0.f, bnext = __ldg(prm + c_b[0] + p.lane);
     const int trole = (tid == 0) ? 1 : 2;
     // One pass of a tile through the network: Fourier features .. output layer; leaves the output layer's
     // pre-activation rows in y13s[par] (visible to all epilogue threads on return).
@@ -700,30 +706,36 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
       PNTF_PUB(0);
       PNTF_PUB(1);
       // encoder: L0 ; {L1, L2(+skip)} ; {L3, L4(+skip)} ; L5 + combine
+      PNTF_BIAS(prm + c_b[1] + p.lane);
       PNTF_WAIT_ACC0();
       if (!first) PNTF_WAIT_SD0();    // X13 of the previous tile
-      epi_hidden_half<C, true, true>(p, ACC_A, ACC_B, p.lane, __ldg(prm + c_b[0] + p.lane), buf1, compat);
+      epi_hidden_half<C, true, true>(p, ACC_A, ACC_B, p.lane, bcur, buf1, compat);
       PNTF_PUB(0);
+      PNTF_BIAS(prm + c_b[2] + p.lane);
       PNTF_WAIT_ACC0();
       PNTF_WAIT_SD0();
-      epi_hidden_half<C, true, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[1] + p.lane), buf0, false);
+      epi_hidden_half<C, true, false>(p, ACC_A, 0, p.lane, bcur, buf0, false);
       PNTF_PUB(0);
+      PNTF_BIAS(prm + c_b[3] + p.lane);
       PNTF_WAIT_ACC0();
       PNTF_WAIT_SD0();
-      epi_hidden_half<C, true, true>(p, ACC_B, ACC_B, p.lane, __ldg(prm + c_b[2] + p.lane), buf1, false);
+      epi_hidden_half<C, true, true>(p, ACC_B, ACC_B, p.lane, bcur, buf1, false);
       PNTF_PUB(0);
+      PNTF_BIAS(prm + c_b[4] + p.lane);
       PNTF_WAIT_ACC0();
       PNTF_WAIT_SD0();
-      epi_hidden_half<C, true, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[3] + p.lane), buf0, false);
+      epi_hidden_half<C, true, false>(p, ACC_A, 0, p.lane, bcur, buf0, false);
       PNTF_PUB(0);
+      PNTF_BIAS(prm + c_b[5] + p.lane);
       PNTF_WAIT_ACC0();
       PNTF_WAIT_SD0();
-      epi_hidden_half<C, true, false>(p, ACC_B, 0, p.lane, __ldg(prm + c_b[4] + p.lane), buf1, false);
+      epi_hidden_half<C, true, false>(p, ACC_B, 0, p.lane, bcur, buf1, false);
       PNTF_PUB(0);
+      PNTF_BIAS(prm + c_b[6] + p.lane);
       PNTF_WAIT_ACC0();
       PNTF_WAIT_SD0();
       PNTF_WAIT_SD1();                // X0's second half (buffer 0)
-      epi_combine<C>(p, ACC_A, ACC_B, __ldg(prm + c_b[5] + p.lane), buf0, TRAIN ? buf1 + kHalfTileBytes : 0u);
+      epi_combine<C>(p, ACC_A, ACC_B, bcur, buf0, TRAIN ? buf1 + kHalfTileBytes : 0u);
       PNTF_PUB(0);
       PNTF_PUB(1);
       // generator: 3 x {La, Lb(+skip)} ; L12 ; L13
@@ -731,37 +743,44 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
       for (int ii = 0; ii < 3; ++ii) {
         const float* ba = prm + c_b[6 + 2 * ii] + p.lane;
         const float* bb = prm + c_b[7 + 2 * ii] + p.lane;
+        PNTF_BIAS(ba + 128);
         PNTF_WAIT_ACC0();
         PNTF_WAIT_SD0();
-        epi_hidden_half<C, false, false>(p, ACC_A, 0, p.lane, __ldg(ba), buf1, false);
+        epi_hidden_half<C, false, false>(p, ACC_A, 0, p.lane, bcur, buf1, false);
         PNTF_PUB(0);
+        PNTF_BIAS(bb);
         PNTF_WAIT_ACC1();
         PNTF_WAIT_SD1();              // ii = 0: the Y5 staging image
-        epi_hidden_half<C, false, false>(p, ACC_A + 128, 0, 128 + p.lane, __ldg(ba + 128), buf1, false);
+        epi_hidden_half<C, false, false>(p, ACC_A + 128, 0, 128 + p.lane, bcur, buf1, false);
         PNTF_PUB(1);
         if (ii < 2) {
+          PNTF_BIAS(bb + 128);
           PNTF_WAIT_ACC0();
           PNTF_WAIT_SD0();
-          epi_hidden_half<C, false, true>(p, ACC_B, ACC_B, p.lane, __ldg(bb), buf0, false);
+          epi_hidden_half<C, false, true>(p, ACC_B, ACC_B, p.lane, bcur, buf0, false);
           PNTF_PUB(0);
+          PNTF_BIAS(prm + c_b[8 + 2 * ii] + p.lane);
           PNTF_WAIT_ACC1();
           PNTF_WAIT_SD1();
-          epi_hidden_half<C, false, true>(p, ACC_B + 128, ACC_B + 128, 128 + p.lane, __ldg(bb + 128), buf0, false);
+          epi_hidden_half<C, false, true>(p, ACC_B + 128, ACC_B + 128, 128 + p.lane, bcur, buf0, false);
           PNTF_PUB(1);
         } else {
+          PNTF_BIAS(bb + 128);
           PNTF_WAIT_ACC0();
           PNTF_WAIT_SD0();
-          epi_hidden_half<C, false, false>(p, ACC_B, 0, p.lane, __ldg(bb), buf0, false);
+          epi_hidden_half<C, false, false>(p, ACC_B, 0, p.lane, bcur, buf0, false);
           PNTF_PUB(0);
+          PNTF_BIAS(prm + c_b[12] + p.lane);
           PNTF_WAIT_ACC1();
           PNTF_WAIT_SD1();
-          epi_hidden_half<C, false, false>(p, ACC_B + 128, 0, 128 + p.lane, __ldg(bb + 128), buf0, false);
+          epi_hidden_half<C, false, false>(p, ACC_B + 128, 0, 128 + p.lane, bcur, buf0, false);
           PNTF_PUB(1);
         }
       }
+      PNTF_BIAS(prm + c_b[0] + p.lane);          // the next tile's first layer
       PNTF_WAIT_ACC0();
       PNTF_WAIT_SD0();
-      epi_hidden_half<C, false, false>(p, ACC_A, 0, p.lane, __ldg(prm + c_b[12] + p.lane), buf1, false);
+      epi_hidden_half<C, false, false>(p, ACC_A, 0, p.lane, bcur, buf1, false);
       PNTF_PUB(0);
       PNTF_WAIT_ACC0();
       // output layer: lane 0 of the accumulator holds y13 for all rows
@@ -968,6 +987,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
 #undef PNTF_WAIT_SD0
 #undef PNTF_WAIT_SD1
 #undef PNTF_PUB
+#undef PNTF_BIAS
   }
   tc_fence_before();
   __syncthreads();
