@@ -190,6 +190,21 @@ int pntf_tc_selftest(const float* W, const float* X, const float* C, float* out,
 int pntf_debug_adjoint_stats(const void* workspace, size_t workspace_bytes, int E, int64_t N, int d, int layer,
                              uint64_t* out, void* stream);
 
+/* Allocation-free path integration.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same computation and outputs as pntf_plan(prec = PNTF_PREC_TC) -- waypoints[Q, max_iter+2, 2d], nsteps[Q], both
+ * caller-provided device buffers -- but the scratch (fp16 weight image, query counter, hand-out order) is a file-scope
+ * __device__ array inside the library: 1 378 560 B (1.31 MiB) that every GPU which loads the library holds until the
+ * process exits.  Limit: Q <= PNTF_PLAN_STATIC_MAX_QUERIES per call; a larger Q returns PNTF_ERR_WORKSPACE and launches
+ * nothing.  The call does not allocate, free or synchronise (first call on a device: one cudaGetSymbolAddress).
+ * All calls on a device share the one array: calls that overlap on the GPU (different streams without an ordering
+ * between them) race on it -- keep them on one stream or order them with events.  Each call rewrites or clears
+ * everything it reads, so nothing carries over from the previous call. */
+#define PNTF_PLAN_STATIC_MAX_QUERIES 65536
+int pntf_plan_static(const float* params, const float* B, const float* start_goal, int64_t Q, int d,
+                     float eta, float thr, int max_iter, int grad_flavour,
+                     float* waypoints, int32_t* nsteps, void* stream);
+
 /* number of kernels the library has launched since load (for bench.py's gpu_launches) */
 int64_t pntf_launch_count(void);
 

@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 #include "../../include/pntf_b200.h"
 #include "tc_api.cuh"
@@ -540,4 +541,62 @@ int tc_loss(int with_grad, int variant, const float* params, const float* B, con
   return finalize_loss(variant, diff, int64_t(E) * N, B, E, d, beta, loss_out, s);
 }
 
+// ---- allocation-free path integration: scratch in a file-scope device array --------------------------------------------
+// pntf_plan_static (include/pntf_b200.h) is pntf_plan(prec = PNTF_PREC_TC) for callers that cannot allocate (code under
+// CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The planner's scratch -- the fp16 weight
+// image, the query counter + distance buckets, the hand-out order of the queries -- lives in g_plan_scratch instead of a
+// caller-provided workspace.  It is sized for PNTF_PLAN_STATIC_MAX_QUERIES queries (1.31 MiB) and every GPU that loads the
+// library holds it until the process exits.
+//
+// In host code the NAME g_plan_scratch is a host-side stand-in for the symbol, not a device address: a kernel handed
+// `g_plan_scratch` from the host faults (or, where the GPU can reach host memory, silently uses the wrong memory).  The
+// device address is asked for once per device with cudaGetSymbolAddress, with that device current, and only that pointer
+// is passed on.
+constexpr size_t kPlanStaticBytes =
+    (kFwdImgBytes + 255) / 256 * 256 + 2048 + size_t(PNTF_PLAN_STATIC_MAX_QUERIES) * 4 + 256;
+static __device__ __align__(256) unsigned char g_plan_scratch[kPlanStaticBytes];
+
+constexpr int kMaxDevices = 64;
+static void* g_plan_scratch_addr[kMaxDevices];     // device address of g_plan_scratch on device i (nullptr: not asked yet)
+static std::mutex g_plan_scratch_mutex;
+
+static int plan_scratch_ptr(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(PNTF_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= kMaxDevices) return fail(PNTF_ERR_UNSUPPORTED, "device ordinal %d beyond %d", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(g_plan_scratch_mutex);
+  if (g_plan_scratch_addr[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_plan_scratch);
+    if (e != cudaSuccess || ptr == nullptr)
+      return fail(PNTF_ERR_CUDA, "cudaGetSymbolAddress(g_plan_scratch) on device %d: %s", dev, cudaGetErrorString(e));
+    g_plan_scratch_addr[dev] = ptr;
+  }
+  *out = g_plan_scratch_addr[dev];
+  return PNTF_OK;
+}
+
 }  // namespace pntf
+
+extern "C" int pntf_plan_static(const float* params, const float* B, const float* start_goal, int64_t Q, int d, float eta,
+                                float thr, int max_iter, int grad_flavour, float* waypoints, int32_t* nsteps,
+                                void* stream) {
+  using namespace pntf;
+  if (!params || !B || (!start_goal && Q > 0)) return fail(PNTF_ERR_ARG, "null pointer argument");
+  if (Q < 0) return fail(PNTF_ERR_ARG, "bad shape Q=%lld", (long long)Q);
+  if (d != 3 && d != 6) return fail(PNTF_ERR_UNSUPPORTED, "dimension d=%d not built (supported: 3, 6)", d);
+  if (!waypoints || !nsteps || max_iter < 0) return fail(PNTF_ERR_ARG, "bad plan argument");
+  if (Q > PNTF_PLAN_STATIC_MAX_QUERIES)
+    return fail(PNTF_ERR_WORKSPACE,
+                "pntf_plan_static: Q=%lld exceeds the built-in scratch (PNTF_PLAN_STATIC_MAX_QUERIES = %d queries per call); "
+                "split the batch or use pntf_plan with a workspace",
+                (long long)Q, PNTF_PLAN_STATIC_MAX_QUERIES);
+  if (Q == 0) return PNTF_OK;
+  void* scratch = nullptr;
+  if (int rc = plan_scratch_ptr(&scratch)) return rc;
+  // tc_plan rewrites the weight image and the hand-out order in full and clears the counters / buckets on `stream`
+  // before the kernels that read them, so nothing of the previous call's contents is used.
+  return tc_plan(params, B, start_goal, Q, d, eta, thr, max_iter, grad_flavour, 1, waypoints, nsteps, scratch,
+                 kPlanStaticBytes, stream);
+}

@@ -20,7 +20,7 @@ GRAD_EXACT, GRAD_COMPAT = 0, 1
 OP_FORWARD, OP_LOSS_FWD, OP_LOSS_BWD, OP_PLAN, OP_FIELD = 0, 1, 2, 3, 4
 
 EXPORTS = ["pntf_version", "pntf_last_error", "pntf_param_offset", "pntf_workspace_bytes", "pntf_forward",
-           "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_loss_fwd_gather", "pntf_loss_bwd_gather", "pntf_loss_bwd_gather_sched", "pntf_adamw", "pntf_adamw_sched", "pntf_plan", "pntf_plan_compact", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end",
+           "pntf_field", "pntf_loss_fwd", "pntf_loss_bwd", "pntf_loss_fwd_gather", "pntf_loss_bwd_gather", "pntf_loss_bwd_gather_sched", "pntf_adamw", "pntf_adamw_sched", "pntf_plan", "pntf_plan_compact", "pntf_plan_static", "pntf_launch_count", "pntf_profile_begin", "pntf_profile_end",
            "pntf_tc_selftest", "pntf_mesh_workspace_bytes", "pntf_mesh_distance", "pntf_debug_adjoint_stats", "pntf_set_deterministic"]
 
 _lib = None
@@ -59,6 +59,7 @@ def lib():
     L.pntf_adamw_sched.argtypes = [c_p, c_p, c_p, c_p, c_p, c_i64, c_p, c_d, c_d, c_d, c_d, c_d, c_p]
     L.pntf_plan.argtypes = [c_p, c_p, c_p, c_i64, c_i, c_f, c_f, c_i, c_i, c_p, c_p, c_i, c_p, c_sz, c_p]
     L.pntf_plan_compact.argtypes = L.pntf_plan.argtypes
+    L.pntf_plan_static.argtypes = [c_p, c_p, c_p, c_i64, c_i, c_f, c_f, c_i, c_i, c_p, c_p, c_p]
     L.pntf_tc_selftest.argtypes = [c_p, c_p, c_p, c_p, c_p]
     L.pntf_debug_adjoint_stats.argtypes = [c_p, c_sz, c_i, c_i64, c_i, c_i, c_p, c_p]
     L.pntf_mesh_workspace_bytes.restype = c_sz
@@ -258,6 +259,22 @@ def plan(params, B, start_goal, d, eta, thr, max_iter, grad_flavour=GRAD_EXACT, 
     _check(fn(_ptr(params, name="params"), _ptr(B, name="B"), _ptr(start_goal, name="start_goal"), Q, d,
               float(eta), float(thr), int(max_iter), grad_flavour, _ptr(way),
               _ptr(nsteps, torch.int32), prec, ws.data_ptr(), ws.numel(), _stream()))
+    return way, nsteps
+
+
+PLAN_STATIC_MAX_QUERIES = 65536      # PNTF_PLAN_STATIC_MAX_QUERIES (include/pntf_b200.h)
+
+
+def plan_static(params, B, start_goal, d, eta, thr, max_iter, way, nsteps, grad_flavour=GRAD_EXACT):
+    """pntf_plan_static: the tensor-core planner with its scratch inside the library.  Allocates nothing -- the caller
+    passes the outputs way[Q, max_iter+2, 2d] (float32) and nsteps[Q] (int32) -- and takes at most
+    PLAN_STATIC_MAX_QUERIES queries per call.  Calls share the scratch: keep them on one stream."""
+    Q = start_goal.shape[0]
+    if way.numel() != Q * (max_iter + 2) * 2 * d or nsteps.numel() != Q:
+        raise ValueError("plan_static: way must hold [Q, max_iter+2, 2d] floats and nsteps [Q] ints")
+    _check(lib().pntf_plan_static(_ptr(params, name="params"), _ptr(B, name="B"), _ptr(start_goal, name="start_goal"),
+                                  Q, d, float(eta), float(thr), int(max_iter), grad_flavour, _ptr(way),
+                                  _ptr(nsteps, torch.int32), _stream()))
     return way, nsteps
 
 
