@@ -438,10 +438,19 @@ __device__ __forceinline__ void mma_block(CTL* ctl, uint32_t ring_addr, uint32_t
 constexpr int kProducerLanes = PNTF_PRODUCER_LANES;
 constexpr int kFwdRing = 5;                 // weight ring depth of the forward kernel
 
+// Second MMA issuer (kernels without a stash, whose I/O warp is otherwise idle): in the 256-feature layers the MMA warp
+// issues output half 0 and the I/O warp output half 1, each on its own accumulator columns and with its own commits; both
+// take their weight stages from the one ring in image order (the MMA warp skips the stages of half 1 and vice versa).
+// In isolation two issuers reach 79 clk per UMMA against 105-113 for one (profiles/r01c_umma_microbench.md, section 6).
+#ifndef PNTF_DUAL_ISSUER
+#define PNTF_DUAL_ISSUER 0
+#endif
+
 template <int D, int ORDER, bool TRAIN, int TAIL>
 __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdArgs a) {
   using C = TcCfg<D, ORDER>;
   constexpr int S = kFwdRing;
+  constexpr bool DUAL = (PNTF_DUAL_ISSUER != 0) && !TRAIN;
   constexpr int CGP = C::CGP, P = C::P;
   constexpr bool PLAN = (TAIL == TC_TAIL_PLAN);
   // who fetches a tile's coordinates: the MMA warp with one bulk copy per tile (COORD_TMA), or -- value-only rows, 64 pairs
@@ -578,6 +587,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
           trace_evt(a.trace, lane_id == 0 && blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x, 0, l, kh);   // operand half kh seen
 #pragma unroll 1
           for (int h = 0; h < MH; ++h) {
+            if (DUAL && h == 1) {       // the second issuer's block: skip its two stages (and drop the look-ahead flag, which
+              it = (it & 0x7fffffffu) + 2;   // would refer to one of them)
+              continue;
+            }
             mma_block<S, !TRAIN>(&ctl, ring_addr, act_addr + (l & 1) * kTileBytes, acc + h * 128, kh, skip || kh > 0, it);
             if (kh == KH - 1) {
               if (elect_one()) umma_commit(&ctl.ar[h]);
@@ -593,6 +606,41 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
       }
     }
   } else if (warp == kIoWarp) {
+    if constexpr (DUAL) {
+      // ----------------------------------------------------------- second MMA issuer: output half 1 of the 256-feature layers
+      // It follows every operand event (also those of the 128-feature layers it has nothing to issue for) so that its
+      // parity counters stay in step; in the layers it issues for, the epilogue cannot publish the next operand tile
+      // before this warp's commit on ar[1], so it is never more than one phase behind xr[].
+      uint32_t it = 0, nx0 = 0, nx1 = 0, npass = 0;
+      const uint32_t ring_addr = smem_u32(ring), act_addr = smem_u32(act);
+      for (int64_t tile = blockIdx.x; PLAN || tile < ntiles; tile += gridDim.x) {
+        if constexpr (PLAN) {
+          mbar_wait(&ctl.go, npass & 1);
+          ++npass;
+          if (!ctl.more) break;
+        }
+#pragma unroll 1
+        for (int l = 0; l < kNumLayers; ++l) {
+          const int KH = c_K[l] >> 7, MH = halves(c_M[l]);
+          const bool skip = c_fwd_skip[l] != 0;
+          const uint32_t acc = tmem_base + (skip ? ACC_B : ACC_A) + 128;
+#pragma unroll 1
+          for (int kh = 0; kh < KH; ++kh) {
+            if (kh == 0) { mbar_spin(&ctl.xr[0], nx0 & 1); ++nx0; }
+            else { mbar_spin(&ctl.xr[1], nx1 & 1); ++nx1; }
+            if (MH == 1) { it += 2; continue; }
+            tc_fence_after();
+            it += 2;                    // the first issuer's block (half 0)
+            mma_block<S, false>(&ctl, ring_addr, act_addr + (l & 1) * kTileBytes, acc, kh, skip || kh > 0, it);
+            it &= 0x7fffffffu;          // the look-ahead flag refers to a stage of the first issuer
+            if (kh == KH - 1) {
+              if (elect_one()) umma_commit(&ctl.ar[1]);
+              __syncwarp();
+            }
+          }
+        }
+      }
+    }
 #ifdef PNTF_HELPER_POLL
     if constexpr (!TRAIN) {
       // helper: follows the producer's stage sequence, observes each `full` barrier and publishes the stage count
