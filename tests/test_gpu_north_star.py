@@ -156,7 +156,15 @@ def test_tc_backward_after_200_optimizer_steps(capi, d, n_train, n_cmp):
     trainer's rules, M:1011,1109, compressed into 200 steps), then: the loss is finite throughout; no operand or adjoint
     tile saturates fp16 (largest magnitudes stay 8x below 65 504 -- before the second-order columns were scaled
     (tc_layers.cuh: kLapScale) X_13 reached 6.5e4 and the loss became inf at step 158 of exactly this run); fewer than
-    half of the adjoints are subnormal; TC parameter gradients agree with fp32 mode and oracle autograd."""
+    half of the adjoints are subnormal; TC parameter gradients agree with fp32 mode and oracle autograd.
+
+    The 200 steps run with deterministic gradient accumulation (pntf_set_deterministic), which makes the trajectory --
+    and so the weights the final comparison is made at -- the same in every run (final loss_n 0.138052 at d = 3,
+    0.106132 at d = 6; worst per-tensor max-norm error 1.9e-2 / 0.5e-2).  With the default fp32 atomics the last bits of
+    the gradients differ from run to run, 200 steps of beta = 1 / loss_n amplify that into different trajectories
+    (final loss_n 0.11 ... 0.33 over three runs, scripts/probe_200step.py) and the error measured on a 200-400 pair
+    slice at whatever weights a run ends at ranged from 0.5e-2 to 6e-2: a property of the end point, not of the kernel,
+    and nothing a fixed bound can be asserted on."""
     from oracle import pntf_oracle as O
     from pntf import synth
     from pntf.model import Model_multi
@@ -168,16 +176,20 @@ def test_tc_backward_after_200_optimizer_steps(capi, d, n_train, n_cmp):
     B = synth.sample_B(d, DEV, seed=1, E=1).contiguous()
     c, s = synth.sample_pairs(n_train, d, DEV, seed=2, margin=0.5 / 12, near_obstacle=True)
     beta, hist = 1.0, []
-    for it in range(200):
-        alpha = 0.5 + 0.5 * it / 199
-        fp.grad.zero_()
-        lo, _ = capi.loss(capi.LOSS_MULTI, fp.flat, B, c, s, 1, n_train, d, alpha, beta, GAMMA, grad_out=fp.grad,
-                          prec=capi.PREC_TC)
-        ln = float(lo[1])
-        assert np.isfinite(ln) and ln > 0, (it, ln)
-        hist.append(ln)
-        opt.step()
-        beta = 1.0 / ln
+    capi.set_deterministic(True)
+    try:
+        for it in range(200):
+            alpha = 0.5 + 0.5 * it / 199
+            fp.grad.zero_()
+            lo, _ = capi.loss(capi.LOSS_MULTI, fp.flat, B, c, s, 1, n_train, d, alpha, beta, GAMMA, grad_out=fp.grad,
+                              prec=capi.PREC_TC)
+            ln = float(lo[1])
+            assert np.isfinite(ln) and ln > 0, (it, ln)
+            hist.append(ln)
+            opt.step()
+            beta = 1.0 / ln
+    finally:
+        capi.set_deterministic(False)
     assert min(hist[100:]) < 0.5 * hist[0]
     # fp16 ranges at the full training batch
     g_full = torch.zeros_like(fp.flat)
