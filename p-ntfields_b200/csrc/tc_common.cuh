@@ -90,6 +90,40 @@ __device__ __forceinline__ void bulk_s2g(void* gmem_dst, const void* smem_src, u
                "r"(bytes)
                : "memory");
 }
+// L2 eviction priority of the stash traffic (-DPNTF_L2_HINTS=0 turns it off).  Every stash line is written once and read
+// once or twice, gigabytes later: it can never hit, but at normal priority it pushes the weight images, biases and
+// coordinates out of L2.  The stash stores of the training forward and the stash loads / Ybar stores of the reverse sweep
+// carry evict_first: same box A/B 15.00 -> 15.42 and 15.85 -> 16.2 M pairs/s (reverse sweep -1.6 ms, forward -0.5 ms per
+// step; profiles/r02q_variants.txt).  The weight-gradient kernel keeps normal priority: the X tiles of the 256-feature
+// layers are read by the two work units (output halves) of the layer at about the same time and the second read must hit
+// (with evict_first on its loads it lost 0.4 ms per step); evict_last on the weight stages adds nothing on top.
+#ifndef PNTF_L2_HINTS
+#define PNTF_L2_HINTS 1
+#endif
+__device__ __forceinline__ uint64_t l2_evict_first() {
+  uint64_t p;
+  asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void stash_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+#if PNTF_L2_HINTS
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "l"(l2_evict_first())
+               : "memory");
+#else
+  bulk_g2s(smem_dst, gmem_src, bytes, bar);
+#endif
+}
+__device__ __forceinline__ void stash_s2g(void* gmem_dst, const void* smem_src, uint32_t bytes) {
+#if PNTF_L2_HINTS
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gmem_dst),
+               "r"(smem_u32(smem_src)), "r"(bytes), "l"(l2_evict_first())
+               : "memory");
+#else
+  bulk_s2g(gmem_dst, smem_src, bytes);
+#endif
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all committed bulk stores have finished READING shared memory
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }

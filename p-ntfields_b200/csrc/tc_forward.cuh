@@ -678,13 +678,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
               else { mbar_wait(&ctl.xio[1][nx1 & 1], (nx1 >> 1) & 1); ++nx1; }
               if (l == 6 && kh == 0) {
                 // encoder outputs Y5, staged by the combine epilogue in the upper half of buffer 1
-                bulk_s2g(a.st.Y5 + size_t(tile) * kHalfTileBytes, act + kTileBytes + kHalfTileBytes, kHalfTileBytes);
+                stash_s2g(a.st.Y5 + size_t(tile) * kHalfTileBytes, act + kTileBytes + kHalfTileBytes, kHalfTileBytes);
                 bulk_commit();
                 bulk_wait_read<0>();
                 mbar_arrive(&ctl.sd[1][ne[1] & 1]);
                 ++ne[1];
               }
-              bulk_s2g(a.st.X[l] + size_t(tile) * K * 256 + size_t(kh) * kHalfTileBytes,
+              stash_s2g(a.st.X[l] + size_t(tile) * K * 256 + size_t(kh) * kHalfTileBytes,
                        act + (l & 1) * kTileBytes + kh * kHalfTileBytes, kHalfTileBytes);
               bulk_commit();
               bulk_wait_read<0>();
@@ -946,7 +946,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
           const Done& r = done[k];
           float* w = a.waypoints + r.q * wstride;
           const int first_e = (r.steps + 1) * 2 * D, last_e = a.fill_tail ? nrow * 2 * D : 0;
-          for (int e = first_e + tid; e < last_e; e += kEpiThreads) w[e] = r.x[e % (2 * D)];
+          for (int e = first_e + tid; e < last_e; e += kEpiThreads) __stcs(w + e, r.x[e % (2 * D)]);   // streaming: never re-read here
           if (tid == 0) a.nsteps[r.q] = r.steps;
         }
       }

@@ -366,7 +366,7 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
       auto load = [&](int l, int64_t tile, int sh, int bh) {
         if (tile >= ntiles) return;
         mbar_arrive_expect_tx(&ctl.yb[bh], kHalfTileBytes);
-        bulk_g2s(xbuf + bh * kHalfTileBytes, src(l, tile) + size_t(sh) * kHalfTileBytes, kHalfTileBytes, &ctl.yb[bh]);
+        stash_g2s(xbuf + bh * kHalfTileBytes, src(l, tile) + size_t(sh) * kHalfTileBytes, kHalfTileBytes, &ctl.yb[bh]);
       };
       // fused backward: flag (tile, l) is published once the bulk group holding the last half of Ybar_l has completed;
       // the check lags two groups behind the newest one, so it never waits for a store that was just issued
@@ -395,7 +395,7 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
             else if (l >= 2) load(l - 2, tile, 0, (l + 1) & 1);
             else if (l == 1) load(12, tn, 0, 0);
             else load(11, tn, 1, 1);
-            bulk_s2g(a.st.G[l] + size_t(tile) * M * 256 + size_t(kh) * kHalfTileBytes, gt + kh * kHalfTileBytes,
+            stash_s2g(a.st.G[l] + size_t(tile) * M * 256 + size_t(kh) * kHalfTileBytes, gt + kh * kHalfTileBytes,
                      kHalfTileBytes);
             bulk_commit();
             bulk_wait_read<0>();
