@@ -185,7 +185,8 @@ int pntf_tc_selftest(const float* W, const float* X, const float* C, float* out,
 /* Test aid for the tensor-core backward (no reference counterpart): statistics of the fp16 adjoint tiles the last
  * pntf_loss_bwd(prec = PNTF_PREC_TC) call left in `workspace` (same E, N, d; the call must have fitted one chunk).
  * Adjoints travel as scaled fp16; layer = -1: all adjoint tiles Ybar_0..12, 0..12: Ybar_layer, 100 + l: the forward
- * operand tile X_l (l = 0..13).  out[4] (device, uint64) = {inf/NaN count, subnormal count, nonzero count, fp32 bit
+ * operand tile X_l (l = 0..13; a library built with -DPNTF_STASH_REGEN regenerates X_0 / X_6 instead of stashing them
+ * and answers PNTF_ERR_ARG for those), 200: the stashed encoder outputs Y5.  out[4] (device, uint64) = {inf/NaN count, subnormal count, nonzero count, fp32 bit
  * pattern of the largest finite magnitude}. */
 int pntf_debug_adjoint_stats(const void* workspace, size_t workspace_bytes, int E, int64_t N, int d, int layer,
                              uint64_t* out, void* stream);

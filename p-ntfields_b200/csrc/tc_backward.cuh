@@ -18,7 +18,7 @@ namespace tc {
 template <int D, int ORDER>
 __global__ void __launch_bounds__(kTcThreads, 1) tc_backward_kernel(const TcRevArgs r, const TcDwArgs w, const int n_rev) {
   if (int(blockIdx.x) < n_rev) tc_reverse_role<D, ORDER>(r, int(blockIdx.x), n_rev);
-  else tc_dw_role(w, int(blockIdx.x) - n_rev);
+  else tc_dw_role<D, ORDER>(w, int(blockIdx.x) - n_rev);
 }
 
 }  // namespace tc

@@ -124,6 +124,10 @@ __device__ __forceinline__ void stash_s2g(void* gmem_dst, const void* smem_src, 
   bulk_s2g(gmem_dst, smem_src, bytes);
 #endif
 }
+// asynchronous prefetch of a global range into L2 (no destination, no completion to wait for)
+__device__ __forceinline__ void bulk_prefetch_l2(const void* gmem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem_src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all committed bulk stores have finished READING shared memory
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }

@@ -149,6 +149,12 @@ __device__ __forceinline__ void st_rows32(uint32_t act_addr, const EpiPos& p, in
 #pragma unroll
   for (int j = 0; j < 4; ++j) sts_chunk(line, f & 7, p.cb + j, v + 8 * j);
 }
+// load the thread's 32 rows of feature f from a tile image in shared memory
+__device__ __forceinline__ void ld_rows32(uint32_t tile_addr, const EpiPos& p, int f, float* v) {
+  const uint32_t line = act_line_addr(tile_addr, f, p.nb);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) lds_chunk(line, f & 7, p.cb + j, v + 8 * j);
+}
 // Epilogue of one 128-feature half of a hidden layer for the thread's 32 rows.
 //   ENC: a pair's CGP columns are two endpoint units of CEP columns (D derivative columns each),
 //   otherwise one unit of CGP columns (2D derivative columns).
@@ -247,13 +253,14 @@ __device__ __forceinline__ void epi_combine(const EpiPos& p, int acc_col, int pr
 }
 
 // Fourier features of both endpoints of the thread's pairs (S:204-210, M:199-213) into the layer-0 operand tile.
-// thread = (frequency k, row quarter).
+// One call = (frequency k, row quarter rq): features k (sin) and 128 + k (cos), 32 rows.  Also used by the weight-gradient
+// kernel, which regenerates this tile instead of reading it from the stash (tc_dw.cuh).
 template <class C>
-__device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>& ts, uint32_t act_addr) {
+__device__ __forceinline__ void fourier_rows(const float* __restrict__ Bmat, const TcTile<C>& ts, int kfreq, int rq, uint32_t act_addr) {
   constexpr int ST = C::STRIDE, EO = C::EOFF, D = C::D;
   EpiPos p;
-  p.lane = threadIdx.x & 127;
-  p.rq = threadIdx.x >> 7;
+  p.lane = kfreq;
+  p.rq = rq;
   p.nb = p.rq >> 1;
   p.cb = (p.rq & 1) * 4;
   p.tmem = 0;
@@ -264,7 +271,7 @@ __device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>
 #pragma unroll
   for (int u = 0; u < C::UPT; ++u) {
     const int pr = p.rq * C::UPT + u;
-    const float* Bp = a.B + int64_t(ts.env[pr]) * D * kNumFreq + k;
+    const float* Bp = Bmat + int64_t(ts.env[pr]) * D * kNumFreq + k;
     float w[D];
 #pragma unroll
     for (int i = 0; i < D; ++i) w[i] = 6.2831855f * __ldg(Bp + i * kNumFreq);
@@ -302,6 +309,11 @@ __device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>
   }
   st_rows32(act_addr, p, k, vs);
   st_rows32(act_addr, p, 128 + k, vc);
+}
+// forward kernels: thread = (frequency, row quarter) over the 512 epilogue threads
+template <class C>
+__device__ __forceinline__ void fourier_tile(const TcFwdArgs& a, const TcTile<C>& ts, uint32_t act_addr) {
+  fourier_rows<C>(a.B, ts, int(threadIdx.x & 127), int(threadIdx.x >> 7), act_addr);
 }
 
 // shared-memory control block
@@ -684,10 +696,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
                 mbar_arrive(&ctl.sd[1][ne[1] & 1]);
                 ++ne[1];
               }
-              stash_s2g(a.st.X[l] + size_t(tile) * K * 256 + size_t(kh) * kHalfTileBytes,
-                       act + (l & 1) * kTileBytes + kh * kHalfTileBytes, kHalfTileBytes);
-              bulk_commit();
-              bulk_wait_read<0>();
+              if (!stash_regen_layer(l)) {   // X_0 and X_6 are regenerated by the weight-gradient kernel (tc_layers.cuh)
+                stash_s2g(a.st.X[l] + size_t(tile) * K * 256 + size_t(kh) * kHalfTileBytes,
+                          act + (l & 1) * kTileBytes + kh * kHalfTileBytes, kHalfTileBytes);
+                bulk_commit();
+                bulk_wait_read<0>();
+              }
               mbar_arrive(&ctl.sd[kh][ne[kh] & 1]);    // this half of the buffer may be overwritten (by the epilogue of layer l+1)
               ++ne[kh];
             }

@@ -71,6 +71,23 @@ struct TcCfg {
   static_assert(EOFF >= CE && STRIDE >= 2 * EOFF && STRIDE >= CG && UPT * STRIDE <= 32, "row packing");
 };
 
+// Operand tiles the training stash need not hold (-DPNTF_STASH_REGEN=bits, bit 0: X_0, bit 1: X_6; OFF by default): X_0, the
+// Fourier features, is a function of the coordinates and X_6, the combine output, of the stashed encoder outputs Y5, and
+// both are read back by the weight-gradient kernel only (the reverse sweep takes its gates from X_{l+1}, l >= 0, and
+// from Y5 at the combine).  With the switch on that kernel regenerates them in shared memory with sixteen otherwise idle
+// warps (tc_dw.cuh): 135 KB of 757 KB of stash stores per tile leave the training forward and 97 KB of 1 311 KB of loads
+// the weight-gradient kernel (ncu: 3.33 -> 3.08 MB of DRAM traffic per tile).  Parity-green (all GPU tests), but slower on
+// the power-capped boxes of this pod (profiles/r02r_variants.txt): the generators need ~2 900 clk per tile
+// and make their work units the stragglers of the launch (17.0 -> 25 ms; 18 ms with a third of the SMs given to them),
+// while the training forward turned out NOT to be write-bound at 1.6-1.7 GHz (no change with both stores removed).
+#ifndef PNTF_STASH_REGEN
+#define PNTF_STASH_REGEN 0
+#endif
+constexpr bool kStashRegen = PNTF_STASH_REGEN != 0;
+__host__ __device__ constexpr bool stash_regen_layer(int l) {
+  return ((PNTF_STASH_REGEN & 1) != 0 && l == 0) || ((PNTF_STASH_REGEN & 2) != 0 && l == 6);
+}
+
 constexpr int kRows = 128;                  // rows (UMMA N) per tile
 constexpr int kTileBytes = 256 * kRows * 2; // activation tile: 256 features x 128 rows fp16
 constexpr int kHalfTileBytes = kTileBytes / 2;

@@ -86,7 +86,7 @@ static int tc_launch_forward(const TcFwdArgs& a_in, cudaStream_t s) {
 // (l = 0..12) and the fp32 output rows
 static size_t stash_tile_bytes() {
   size_t s = 0;
-  for (int l = 0; l <= 13; ++l) s += size_t(layer_desc(l).K) * 256;
+  for (int l = 0; l <= 13; ++l) s += stash_regen_layer(l) ? 0 : size_t(layer_desc(l).K) * 256;   // X_0, X_6: regenerated (tc_layers.cuh)
   for (int l = 0; l <= 12; ++l) s += size_t(layer_desc(l).M) * 256;
   return s + kHalfTileBytes + kRows * sizeof(float) + kFlagStride * sizeof(uint32_t);
 }
@@ -143,7 +143,10 @@ size_t tc_workspace_bytes(int op, int E, int64_t N, int d, size_t budget_bytes) 
 
 static void tc_carve_stash(TcStash& st, uint8_t* base, size_t tiles) {
   size_t off = 0;
-  for (int l = 0; l <= 13; ++l) { st.X[l] = base + off; off += tiles * layer_desc(l).K * 256; }
+  for (int l = 0; l <= 13; ++l) {
+    if (stash_regen_layer(l)) { st.X[l] = nullptr; continue; }
+    st.X[l] = base + off; off += tiles * layer_desc(l).K * 256;
+  }
   for (int l = 0; l <= 12; ++l) { st.G[l] = base + off; off += tiles * layer_desc(l).M * 256; }
   st.G[13] = nullptr;
   st.Y5 = base + off; off += tiles * kHalfTileBytes;
@@ -152,20 +155,35 @@ static void tc_carve_stash(TcStash& st, uint8_t* base, size_t tiles) {
 // per-(tile, layer) flags of the fused backward launch: behind the y13 rows
 static uint32_t* stash_flags(const TcStash& st, size_t tiles) { return reinterpret_cast<uint32_t*>(st.y13 + tiles * kRows); }
 
-// work units of the weight-gradient kernel: (layer, 128-feature half), CTAs proportional to the bytes a
-// unit streams per tile (32 KB of Ybar + K*256 B of X)
+// work units of the weight-gradient kernel: (layer, 128-feature half); every SM gets a CTA, shared out in proportion to
+// the cost of a unit per tile: the KB it streams (32 KB of Ybar + K*256 B of X), or, for the units that regenerate their
+// X operand (layers 0 and 6 with kStashRegen, tc_dw.cuh), a cost that stands for the generator's time per tile
+// (PNTF_DW_GEN_COST, in the same KB units; measured default below)
 static DwUnits make_dw_units(int sms) {
+  static const int gen_cost = [] {
+    const char* e = getenv("PNTF_DW_GEN_COST");
+    const int v = e != nullptr ? atoi(e) : 0;
+    return v > 0 ? v : 64;
+  }();
   DwUnits u{};
-  int n = 0, cta = 0;
+  int n = 0;
+  int cost[kDwMaxUnits], cnt[kDwMaxUnits];
   for (int l = 0; l <= 12; ++l)
     for (int h = 0; h < (layer_desc(l).M + 127) / 128; ++h) {
-      u.l[n] = l; u.h[n] = h; u.cta_begin[n] = cta;
-      int c = (layer_desc(l).K == 256) ? 8 : 6;
-      if (sms < 142) c = (c * sms) / 142 > 0 ? (c * sms) / 142 : 1;
-      cta += c;
+      u.l[n] = l; u.h[n] = h;
+      cost[n] = stash_regen_layer(l) ? gen_cost : 32 + layer_desc(l).K / 4;
+      cnt[n] = 1;
       ++n;
     }
   u.n = n;
+  for (int extra = sms - n; extra > 0; --extra) {
+    int best = 0;
+    for (int i = 1; i < n; ++i)
+      if (cost[i] * cnt[best] > cost[best] * cnt[i]) best = i;   // largest cost per CTA
+    ++cnt[best];
+  }
+  int cta = 0;
+  for (int i = 0; i < n; ++i) { u.cta_begin[i] = cta; cta += cnt[i]; }
   u.cta_begin[n] = cta;
   return u;
 }
@@ -241,7 +259,8 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
   const size_t smem_d = size_t(kDwStages) * kDwStageBytes + 1024;
   if (int rc = tc_set_smem(kf, smem_f)) return rc;
   if (int rc = tc_set_smem(kr, smem_r)) return rc;
-  if (int rc = tc_set_smem(tc_dw_kernel, smem_d)) return rc;
+  auto kd = tc_dw_kernel<D, ORDER>;
+  if (int rc = tc_set_smem(kd, smem_d)) return rc;
   static_assert(kRevSmem >= size_t(kDwStages) * kDwStageBytes + 1024, "the fused launch uses the reverse sweep's shared memory size");
   if (int rc = tc_set_smem(kb, smem_r)) return rc;
   const int n_dw = fused_dw_ctas(chunk_tiles);
@@ -272,6 +291,8 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     a.trace = nullptr;
     if (int rc = launch_check("tc_forward(train)")) return rc;
     TcDwArgs dw{};
+    dw.rg.B = a.B; dw.rg.coords = a.coords; dw.rg.index = a.index; dw.rg.cstride = a.cstride;
+    dw.rg.n_total = a.n_total; dw.rg.n_per_env = a.n_per_env; dw.rg.pair_begin = a.pair_begin; dw.rg.pair_count = a.pair_count;
     dw.st = a.st; dw.units = units; dw.ntiles = tiles; dw.grad = grad_params; dw.out_scale = out_scale;
     dw.sched = a.sched; dw.inv_scale = r.inv_scale; dw.detw = detw;
     if (n_dw > 0) {
@@ -299,7 +320,7 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
     a.trace = nullptr;
     if (int rc = launch_check("tc_reverse")) return rc;
     prof_start(KC_TC_DW, s);
-    tc_dw_kernel<<<units.cta_begin[units.n], kDwThreads, smem_d, s>>>(dw);
+    kd<<<units.cta_begin[units.n], kDwThreads, smem_d, s>>>(dw);
     prof_stop(s);
     if (int rc = launch_check("tc_dw")) return rc;
   }
@@ -331,7 +352,8 @@ __global__ void adjoint_stats_kernel(const __half* __restrict__ g, size_t n, uns
   atomicMax(reinterpret_cast<unsigned int*>(out + 3), __float_as_uint(mx));
 }
 
-// layer < 0: all adjoint tiles Ybar_0..12; layer = 100 + l: the forward operand tile X_l (l = 0..13) instead
+// layer < 0: all adjoint tiles Ybar_0..12; layer = 100 + l: the forward operand tile X_l (l = 0..13) instead (X_0 and X_6
+// are not stashed when kStashRegen: PNTF_ERR_ARG); layer = 200: the encoder outputs Y5, from which X_6 is regenerated
 int tc_debug_adjoint_stats(const void* workspace, size_t workspace_bytes, int E, int64_t N, int d, int layer,
                            unsigned long long* out, void* stream) {
   const size_t P = tc_tile_pairs(d);
@@ -345,7 +367,12 @@ int tc_debug_adjoint_stats(const void* workspace, size_t workspace_bytes, int E,
   if (e != cudaSuccess) return fail(PNTF_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
   const uint8_t* base = st.G[0];
   size_t bytes = 0;
-  if (layer >= 100 && layer <= 113) {
+  if (layer == 200) {
+    base = st.Y5;
+    bytes = ntiles * size_t(kHalfTileBytes);
+  } else if (layer >= 100 && layer <= 113) {
+    if (stash_regen_layer(layer - 100))
+      return fail(PNTF_ERR_ARG, "X_%d is not stashed: the weight-gradient kernel regenerates it", layer - 100);
     base = st.X[layer - 100];
     bytes = ntiles * size_t(layer_desc(layer - 100).K) * 256;
   } else if (layer >= 0 && layer <= 12) {

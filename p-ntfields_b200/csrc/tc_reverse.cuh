@@ -102,12 +102,6 @@ __device__ __forceinline__ void act_adjoint_unit(float* g, const float* x) {
   g[0] = xb;
 }
 
-// load the thread's 32 rows of feature f from a stash tile image in shared memory
-__device__ __forceinline__ void ld_rows32(uint32_t tile_addr, const EpiPos& p, int f, float* v) {
-  const uint32_t line = act_line_addr(tile_addr, f, p.nb);
-#pragma unroll
-  for (int j = 0; j < 4; ++j) lds_chunk(line, f & 7, p.cb + j, v + 8 * j);
-}
 
 // Ybar_l for one 128-feature half of a hidden layer, the thread's 32 rows.  SRC13: the incoming adjoint
 // is the rank-1 product w13[f] * g13[row] (output layer) instead of a TMEM accumulator; its weight

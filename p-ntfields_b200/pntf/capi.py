@@ -295,7 +295,8 @@ def mesh_distance(triangles, points, offset=None, margin=None):
 def adjoint_stats(E, N, d, budget=0, layer=-1):
     """{inf_nan, subnormal, nonzero, max_abs} of the fp16 adjoint tiles left in the cached workspace by the last
     loss(..., grad_out=..., prec=PREC_TC) call of the same shape (adjoints carry the library's scale).  layer = -1: all
-    adjoint tiles, 0..12: Ybar_layer, 100 + l: the forward operand tile X_l."""
+    adjoint tiles, 0..12: Ybar_layer, 100 + l: the forward operand tile X_l (a -DPNTF_STASH_REGEN build does not
+    stash X_0 / X_6 and raises for them), 200: the stashed encoder outputs Y5."""
     import struct
     dev = torch.device("cuda", torch.cuda.current_device())
     ws = workspace(workspace_bytes(OP_LOSS_BWD, E, N, d, PREC_TC, budget), dev)

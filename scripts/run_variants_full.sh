@@ -12,7 +12,13 @@ import json, sys
 t = sys.argv[1]
 try:
     j = json.loads(open("gpurun_out/varf_%s.json" % t).read().strip().splitlines()[-1])
-    k = j["kernels"]; f = j["extra"]["fields"]; p = j["extra"]["plan"]["exact_tc"]
+    k = j["kernels"]
+    if "extra" not in j:      # --no-plan: training step only
+        print("%-8s %.3f M pairs/s fwd %.2f rev %.2f dw %.2f | loss %.6f | %d MHz" % (
+            t, j["value"] / 1e6, k["tc_forward"]["ms_per_step"], k["tc_reverse"]["ms_per_step"], k["tc_dw"]["ms_per_step"],
+            j["final_loss_n"], j["clocks"]["sm_mhz"]))
+        raise SystemExit
+    f = j["extra"]["fields"]; p = j["extra"]["plan"]["exact_tc"]
     print("%-8s %.3f M pairs/s fwd %.2f rev %.2f dw %.2f | plan %.3f M paths/s | TT %.1f speed %.1f speed2 %.1f lap %.1f M/s | loss %.6f | %d MHz" % (
         t, j["value"] / 1e6, k["tc_forward"]["ms_per_step"], k["tc_reverse"]["ms_per_step"], k["tc_dw"]["ms_per_step"],
         p["paths_per_s"] / 1e6, f["travel_times_pairs_per_s"] / 1e6, f["speed_pairs_per_s"] / 1e6, f["speed2_pairs_per_s"] / 1e6,

@@ -197,8 +197,12 @@ def test_tc_backward_after_200_optimizer_steps(capi, d, n_train, n_cmp):
     st = capi.adjoint_stats(1, n_train, d)
     assert st["inf_nan"] == 0 and st["max_abs"] < 65504 / 8, st
     assert st["subnormal"] < 0.5 * st["nonzero"], st
-    for l in range(14):
-        sx = capi.adjoint_stats(1, n_train, d, layer=100 + l)
+    for l in list(range(14)) + [100]:    # 100 + 100 = layer 200: the encoder outputs Y5
+        try:
+            sx = capi.adjoint_stats(1, n_train, d, layer=100 + l)
+        except RuntimeError as e:        # a -DPNTF_STASH_REGEN build regenerates X_0 / X_6 instead of stashing them
+            assert l in (0, 6) and "not stashed" in str(e), (l, e)
+            continue
         assert sx["inf_nan"] == 0 and sx["max_abs"] < 65504 / 8, (l, sx)
     assert bool(torch.isfinite(g_full).all())
     # gradients on a slice the oracle can differentiate
