@@ -356,7 +356,7 @@ def roofline_of(ctx, prof, d, n_total, steps, ms_total):
     per_pair = per_tile / LOSS_PAIRS_PER_TILE[d] if per_tile else None
     pairs_per_launch = n_total * steps / max(top_cnt, 1)
     alg_bytes_pair = 2 * d * 4 + 8 + 4
-    return {"bound": "tensor", "limiter": "hbm (the activation stash) at full clocks; shared-memory bandwidth of the MMA phases + the serial MMA->epilogue chain under the power cap (DESIGN.md section 7b)", "kernel": top_name,
+    return {"bound": "tensor", "limiter": "hbm (the activation stash) at full clocks; board power (energy per step) and the serial MMA->epilogue chain under a power cap (DESIGN.md section 7b)", "kernel": top_name,
             "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
             "traffic": per_pair * pairs_per_launch if per_pair else None, "traffic_source": src if per_pair else None,
             "dram_bytes_per_pair": per_pair, "algorithmic_bytes_per_pair": alg_bytes_pair,

@@ -251,6 +251,15 @@ static int tc_loss_bwd(int variant, const float* params, const float* B, const f
   }
   const int64_t ntiles_all = (n_total + C::P - 1) / C::P;
   if (chunk_tiles > ntiles_all) chunk_tiles = ntiles_all;
+  else {
+    // several chunks: equal sizes, rounded up to whole waves of the persistent kernels (every CTA of the forward and the
+    // reverse sweep then owns the same number of tiles; only the last chunk is ragged)
+    const int64_t sms = sm_count(), nchunks = (ntiles_all + chunk_tiles - 1) / chunk_tiles;
+    int64_t per = (ntiles_all + nchunks - 1) / nchunks;
+    per = (per + sms - 1) / sms * sms;
+    if (per <= chunk_tiles) chunk_tiles = per;
+    else if (chunk_tiles >= sms) chunk_tiles -= chunk_tiles % sms;
+  }
   if (int rc = tc_pack(params, fimg, rimg, s)) return rc;
   auto kf = tc_forward_kernel<D, ORDER, true, TC_TAIL_LOSS>;
   auto kr = tc_reverse_kernel<D, ORDER>;
