@@ -124,6 +124,12 @@ __device__ __forceinline__ void stash_s2g(void* gmem_dst, const void* smem_src, 
   bulk_s2g(gmem_dst, smem_src, bytes);
 #endif
 }
+// 4-byte asynchronous copy global -> shared (LDGSTS: no register holds the value while it is in flight); a thread sees its
+// own copies after cp_async_wait_all()
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 // asynchronous prefetch of a global range into L2 (no destination, no completion to wait for)
 __device__ __forceinline__ void bulk_prefetch_l2(const void* gmem_src, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem_src), "r"(bytes) : "memory");

@@ -968,7 +968,31 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
         ctl.more = 0;
         mbar_arrive(&ctl.go);
       }
-    } else
+    } else {
+    // TC_TAIL_LOSS: the observed speeds of a tile reach shared memory one tile ahead of the tail that uses them (and the
+    // gather index, if any, two tiles ahead), by asynchronous copies that occupy no registers: a global round trip in the
+    // tail delays warp 0's share of the next tile's Fourier features and with it the whole next tile.  Neutral on the
+    // power-capped (energy-limited) boxes this was measured on (profiles/r02v_tail_loads.txt); kept for boards that run
+    // at full clocks, where the forward is bound by this chain.
+    constexpr bool SPEED_AHEAD = (TAIL == TC_TAIL_LOSS && ORDER >= 2);
+    __shared__ float spd_s[2][P][2];
+    __shared__ int32_t row_s[2][P];
+    auto pair_of = [&](int64_t tile) -> int64_t {     // this thread's pair in `tile`, or -1
+      const int64_t pr = a.pair_begin + tile * P + tid;
+      return (tile < ntiles && pr < a.pair_begin + a.pair_count && pr < a.n_total) ? pr : -1;
+    };
+    auto fetch_speed = [&](int64_t pr, int64_t row, int buf) {
+      if (pr < 0) return;
+      cp_async4(&spd_s[buf][tid][0], a.speed + row * a.sstride);
+      cp_async4(&spd_s[buf][tid][1], a.speed + row * a.sstride + 1);
+    };
+    if constexpr (SPEED_AHEAD) {
+      if (tid < P) {
+        const int64_t p0 = pair_of(blockIdx.x), p1 = pair_of(int64_t(blockIdx.x) + gridDim.x);
+        fetch_speed(p0, p0 >= 0 ? src_row(a, p0) : 0, 0);
+        if (a.index != nullptr && p1 >= 0) cp_async4(&row_s[1][tid], a.index + p1);
+      }
+    }
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1) {
       const int64_t pair0 = a.pair_begin + tile * P;
       pass(tile == int64_t(blockIdx.x), par, blockIdx.x == 0 && tile == int64_t(blockIdx.x) + 2 * gridDim.x);
@@ -976,6 +1000,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
         if (tid >= 128 && tid < 128 + kRows) a.st.y13[size_t(tile) * kRows + (tid - 128)] = y13s[par][tid - 128];
       }
       if (tid < P) {
+        if constexpr (SPEED_AHEAD) cp_async_wait_all();   // this tile's speeds and the next tile's gather index (issued a tile ago)
         if (ts[par].valid[tid]) {
           const int64_t pair = pair0 + tid;
           if constexpr (ORDER == 0) {
@@ -1018,10 +1043,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
           }
           const float* x = ts[par].x[tid];
           if constexpr (TAIL == TC_TAIL_LOSS && ORDER >= 2) {
-            const float* sp = a.speed + src_row(a, pair) * a.sstride;
             const float al = sched_alpha(a);
-            const float y0 = al * __ldg(sp) + 1.0f - al;
-            const float y1 = al * __ldg(sp + 1) + 1.0f - al;
+            const float y0 = al * spd_s[par][tid][0] + 1.0f - al;      // landed: cp_async_wait_all() above
+            const float y1 = al * spd_s[par][tid][1] + 1.0f - al;
             a.diff[pair] = eikonal_residual<D, false>(x, tau, dtau, ltau, y0, y1, sched_gamma(a), a.single_variant, 0.f, nullptr,
                                                       nullptr, nullptr);
           }
@@ -1042,7 +1066,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
         // this buffer's next user is the tile after next: COORD_TMA -> the MMA warp refills it (load_coords); else fetch
         // its coordinates now (the barrier of the next tile orders these writes before its readers)
         if constexpr (!COORD_TMA) load_tile(tile + 2 * int64_t(gridDim.x), ts[par]);
+        if constexpr (SPEED_AHEAD) {
+          const int64_t pn = pair_of(tile + gridDim.x), pn2 = pair_of(tile + 2 * int64_t(gridDim.x));
+          fetch_speed(pn, (a.index != nullptr && pn >= 0) ? int64_t(row_s[par ^ 1][tid]) : pn, par ^ 1);
+          if (a.index != nullptr && pn2 >= 0) cp_async4(&row_s[par][tid], a.index + pn2);
+        }
       }
+    }
     }
 #undef PNTF_WAIT_ACC0
 #undef PNTF_WAIT_ACC1

@@ -420,7 +420,35 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
     long long* const detb = b.detb != nullptr ? b.detb + size_t(cta) * kDetSlots : nullptr;
     float dw13 = 0.f, unused = 0.f;
     uint32_t nar0 = 0, nar1 = 0, ny0 = 0, ny1 = 0, nsd0 = 0, nsd1 = 0;
-    for (int64_t tile = cta; tile < ntiles; tile += ncta) {
+    // The inputs of a tile's loss seeds (coordinates, output-layer rows, observed speeds of this thread's pair) reach shared
+    // memory one tile ahead of their use, the gather index two tiles ahead, by asynchronous copies that occupy no registers:
+    // every epilogue thread waits for the seeds at the named barrier below, so a global round trip here is a gap in every
+    // tile.  Neutral on the power-capped (energy-limited) boxes this was measured on (profiles/r02v_tail_loads.txt); kept
+    // for boards that run at full clocks, where the sweep is bound by this chain.
+    constexpr int kSeedIn = 2 * D + C::CG + 2;
+    __shared__ float seed_s[2][P][kSeedIn];
+    __shared__ int32_t srow_s[2][P];
+    auto pair_of = [&](int64_t tile) -> int64_t {     // this thread's pair in `tile`, or -1
+      const int64_t pr = a.pair_begin + tile * P + tid;
+      return (tile < ntiles && pr < a.pair_begin + a.pair_count && pr < a.n_total) ? pr : -1;
+    };
+    auto fetch_seed = [&](int64_t tile, int64_t pr, int64_t row, int buf) {
+      if (pr < 0) return;
+      float* dst = seed_s[buf][tid];
+#pragma unroll
+      for (int i = 0; i < 2 * D; ++i) cp_async4(dst + i, a.coords + row * a.cstride + i);
+#pragma unroll
+      for (int c = 0; c < C::CG; ++c) cp_async4(dst + 2 * D + c, a.st.y13 + size_t(tile) * kRows + C::pair_row(tid) + c);
+      cp_async4(dst + 2 * D + C::CG, a.speed + row * a.sstride);
+      cp_async4(dst + 2 * D + C::CG + 1, a.speed + row * a.sstride + 1);
+    };
+    if (tid < P) {
+      const int64_t p0 = pair_of(cta), p1 = pair_of(int64_t(cta) + ncta);
+      fetch_seed(cta, p0, p0 >= 0 ? src_row(a, p0) : 0, 0);
+      if (a.index != nullptr && p1 >= 0) cp_async4(&srow_s[1][tid], a.index + p1);
+    }
+    int spar = 0;
+    for (int64_t tile = cta; tile < ntiles; tile += ncta, spar ^= 1) {
       const int64_t pair0 = a.pair_begin + tile * P;
       int tl = 12;
       const bool tron = tid == 0 && cta == 0 && tile == int64_t(cta) + 2 * ncta;
@@ -431,13 +459,14 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
         float gy[CGP];
 #pragma unroll
         for (int c = 0; c < CGP; ++c) gy[c] = 0.f;
+        cp_async_wait_all();     // this tile's seed inputs and the next tile's gather index (issued a tile ago)
         if (valid) {
           float x[2 * D], y[CGP];
-          const int64_t srow = src_row(a, pair);
+          const float* sin_ = seed_s[spar][tid];
 #pragma unroll
-          for (int i = 0; i < 2 * D; ++i) x[i] = __ldg(a.coords + srow * a.cstride + i);
+          for (int i = 0; i < 2 * D; ++i) x[i] = sin_[i];
 #pragma unroll
-          for (int c = 0; c < C::CG; ++c) y[c] = a.st.y13[size_t(tile) * kRows + C::pair_row(tid) + c];
+          for (int c = 0; c < C::CG; ++c) y[c] = sin_[2 * D + c];
           y[0] += __ldg(prm + c_b[13]);
           const ActOut o = actout_eval(y[0]);
           float dtau[NG], ltau[NG];
@@ -457,8 +486,8 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
             }
           }
           const float al = sched_alpha(a);
-          const float y0 = al * __ldg(a.speed + srow * a.sstride) + 1.0f - al;
-          const float y1 = al * __ldg(a.speed + srow * a.sstride + 1) + 1.0f - al;
+          const float y0 = al * sin_[2 * D + C::CG] + 1.0f - al;
+          const float y1 = al * sin_[2 * D + C::CG + 1] + 1.0f - al;
           float tb, dbar[NG], lbar[NG];
           eikonal_residual<D, true>(x, o.o, dtau, ltau, y0, y1, sched_gamma(a), a.single_variant, kGradScale, &tb, dbar, lbar);
           float yb = tb * o.o1;
@@ -491,6 +520,10 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
         }
 #pragma unroll
         for (int c = 0; c < C::STRIDE; ++c) g13s[C::pair_row(tid) + c] = gy[c];
+        // the next tile's seed inputs, and the gather index of the tile after it
+        const int64_t tn = tile + ncta, pn = pair_of(tn), pn2 = pair_of(tile + 2 * int64_t(ncta));
+        fetch_seed(tn, pn, (a.index != nullptr && pn >= 0) ? int64_t(srow_s[spar ^ 1][tid]) : pn, spar ^ 1);
+        if (a.index != nullptr && pn2 >= 0) cp_async4(&srow_s[spar][tid], a.index + pn2);
       }
       named_bar_sync(1, kEpiThreads);
       // product half ready (adjoint input, and the product is done reading operand-tile half h), the stash store of
