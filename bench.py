@@ -237,8 +237,9 @@ class ClockSampler:
         # "under load" = samples with power in the upper half of what was seen
         thr = 0.5 * (max(pw) + min(pw))
         load = [s for s, p in zip(sm, pw) if p >= thr] or sm
+        pw_load = [p for p in pw if p >= thr] or pw
         return {"sm_mhz": statistics.median(load), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm),
-                "power_w_max": max(pw)}
+                "power_w_max": max(pw), "power_w": statistics.median(pw_load)}
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -404,6 +405,9 @@ def run_b200(args):
     launches = capi.launch_count() - launches0
     clocks = sampler.stop() if rank == 0 else None
     ms_per_step = ms_total / args.steps
+    if clocks and clocks.get("power_w"):
+        # board power under load x step time: under a board power cap the step is energy-limited
+        clocks["energy_j_per_step"] = clocks["power_w"] * ms_per_step * 1e-3
     value = world * t.n_total * args.steps / (ms_total * 1e-3)
     prof = kernel_profile(ctx, t.step, args.steps)
     final_loss = float(t.fp.loss_slot[1].item())
