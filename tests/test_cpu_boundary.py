@@ -156,3 +156,35 @@ def test_gradient_allreduce_gloo_world2(tmp_path):
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
         assert "ok" in o
+
+
+def test_bench_reads_committed_traffic_table_and_parses_power_samples(tmp_path):
+    """bench.py's roofline.traffic comes from the newest committed ncu capture (no constants in bench.py), and the clocks
+    block is computed from nvidia-smi samples: under-load median clock, throttle reasons, board power, for the energy
+    per step."""
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("pntf_bench", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    table, src = bench.dram_bytes_per_tile()
+    assert src is not None and src.startswith("profiles/") and src.endswith("dram_bytes_per_tile.json")
+    for k in ("tc_forward", "tc_reverse", "tc_dw"):
+        assert 2e5 < table[k] < 2e6, (k, table[k])          # a few hundred KB per 128-row tile and kernel
+    s = bench.ClockSampler(0)
+    s.path = str(tmp_path / "clocks.csv")
+    with open(s.path, "w") as f:
+        f.write("0, 1965, 1965, 180.0, 0x0, Not Active, Not Active, Not Active, Not Active\n")
+        f.write("0, 1620, 1965, 590.0, 0x4, Not Active, Not Active, Not Active, Active\n")
+        f.write("0, 1590, 1965, 600.0, 0x4, Not Active, Not Active, Not Active, Active\n")
+        f.write("garbage line\n")
+
+    class _P:
+        def terminate(self): pass
+        def wait(self, timeout=None): return 0
+        def kill(self): pass
+    s.proc, s.f = _P(), open(os.devnull, "w")
+    c = s.stop()
+    assert c["sm_mhz"] == 1605.0 and c["sm_max_mhz"] == 1965.0 and c["reasons"] == ["sw_power_cap"]
+    assert c["power_w_max"] == 600.0 and c["power_w"] == 595.0 and c["samples"] == 3
