@@ -188,8 +188,11 @@ def workload_config(args, prec):
 # clocks sampling
 # ---------------------------------------------------------------------------------------------------
 class ClockSampler:
+    # power.draw is a ~1 s average and under-reads a sub-second timed region (it showed 550-620 W where the board sat at its
+    # 1000 W limit: scripts/power_probe.sh); power.draw.instant, the last column, is what the power fields are taken from
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,"
+         "power.draw.instant")
 
     def __init__(self, index):
         self.index = index
@@ -225,6 +228,10 @@ class ClockSampler:
                     pw.append(float(parts[3]))
                 except ValueError:
                     continue
+                try:
+                    pw[-1] = float(parts[9])
+                except (ValueError, IndexError):
+                    pass
                 for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[5:9]):
                     if val.lower().startswith("active"):
                         reasons.add(name)

@@ -971,9 +971,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_forward_kernel(const TcFwdAr
     } else {
     // TC_TAIL_LOSS: the observed speeds of a tile reach shared memory one tile ahead of the tail that uses them (and the
     // gather index, if any, two tiles ahead), by asynchronous copies that occupy no registers: a global round trip in the
-    // tail delays warp 0's share of the next tile's Fourier features and with it the whole next tile.  Neutral on the
-    // power-capped (energy-limited) boxes this was measured on (profiles/r02v_tail_loads.txt); kept for boards that run
-    // at full clocks, where the forward is bound by this chain.
+    // tail delays warp 0's share of the next tile's Fourier features and with it the whole next tile.  Neutral for the
+    // 1 Mi-pair step, which is limited by the board's power budget (profiles/r02v_tail_loads.txt); kept for the cases that
+    // leave power to spare, where the forward is bound by this chain.
     constexpr bool SPEED_AHEAD = (TAIL == TC_TAIL_LOSS && ORDER >= 2);
     __shared__ float spd_s[2][P][2];
     __shared__ int32_t row_s[2][P];

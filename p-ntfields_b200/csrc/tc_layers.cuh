@@ -77,7 +77,7 @@ struct TcCfg {
 // from Y5 at the combine).  With the switch on that kernel regenerates them in shared memory with sixteen otherwise idle
 // warps (tc_dw.cuh): 135 KB of 757 KB of stash stores per tile leave the training forward and 97 KB of 1 311 KB of loads
 // the weight-gradient kernel (ncu: 3.33 -> 3.08 MB of DRAM traffic per tile).  Parity-green (all GPU tests), but slower on
-// the power-capped boxes of this pod (profiles/r02r_variants.txt): the generators need ~2 900 clk per tile
+// the power-limited 1 Mi-pair step (profiles/r02r_variants.txt): the generators need ~2 900 clk per tile
 // and make their work units the stragglers of the launch (17.0 -> 25 ms; 18 ms with a third of the SMs given to them),
 // while the training forward turned out NOT to be write-bound at 1.6-1.7 GHz (no change with both stores removed).
 #ifndef PNTF_STASH_REGEN

@@ -423,8 +423,8 @@ __device__ __forceinline__ void tc_reverse_role(const TcRevArgs& b, const int ct
     // The inputs of a tile's loss seeds (coordinates, output-layer rows, observed speeds of this thread's pair) reach shared
     // memory one tile ahead of their use, the gather index two tiles ahead, by asynchronous copies that occupy no registers:
     // every epilogue thread waits for the seeds at the named barrier below, so a global round trip here is a gap in every
-    // tile.  Neutral on the power-capped (energy-limited) boxes this was measured on (profiles/r02v_tail_loads.txt); kept
-    // for boards that run at full clocks, where the sweep is bound by this chain.
+    // tile.  Neutral for the 1 Mi-pair step, which is limited by the board's power budget (profiles/r02v_tail_loads.txt); kept
+    // for the cases that leave power to spare, where the sweep is bound by this chain.
     constexpr int kSeedIn = 2 * D + C::CG + 2;
     __shared__ float seed_s[2][P][kSeedIn];
     __shared__ int32_t srow_s[2][P];

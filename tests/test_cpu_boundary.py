@@ -175,9 +175,9 @@ def test_bench_reads_committed_traffic_table_and_parses_power_samples(tmp_path):
     s = bench.ClockSampler(0)
     s.path = str(tmp_path / "clocks.csv")
     with open(s.path, "w") as f:
-        f.write("0, 1965, 1965, 180.0, 0x0, Not Active, Not Active, Not Active, Not Active\n")
-        f.write("0, 1620, 1965, 590.0, 0x4, Not Active, Not Active, Not Active, Active\n")
-        f.write("0, 1590, 1965, 600.0, 0x4, Not Active, Not Active, Not Active, Active\n")
+        f.write("0, 1965, 1965, 180.0, 0x0, Not Active, Not Active, Not Active, Not Active, 185.0\n")
+        f.write("0, 1620, 1965, 590.0, 0x4, Not Active, Not Active, Not Active, Active, 980.0\n")
+        f.write("0, 1590, 1965, 600.0, 0x4, Not Active, Not Active, Not Active, Active, [N/A]\n")   # falls back to power.draw
         f.write("garbage line\n")
 
     class _P:
@@ -187,4 +187,4 @@ def test_bench_reads_committed_traffic_table_and_parses_power_samples(tmp_path):
     s.proc, s.f = _P(), open(os.devnull, "w")
     c = s.stop()
     assert c["sm_mhz"] == 1605.0 and c["sm_max_mhz"] == 1965.0 and c["reasons"] == ["sw_power_cap"]
-    assert c["power_w_max"] == 600.0 and c["power_w"] == 595.0 and c["samples"] == 3
+    assert c["power_w_max"] == 980.0 and c["power_w"] == 790.0 and c["samples"] == 3
