@@ -201,6 +201,14 @@ class ClockSampler:
 
     def start(self):
         try:
+            # a driver without the instantaneous field would reject the whole query: probe it once, outside the timed region
+            probe = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=power.draw.instant", "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=20)
+            if probe.returncode != 0 or "not a valid field" in (probe.stdout + probe.stderr).lower():
+                self.Q = self.Q.rsplit(",", 1)[0]
+        except (OSError, subprocess.SubprocessError):
+            pass
+        try:
             self.f = open(self.path, "w")
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
                                           "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
