@@ -188,8 +188,9 @@ def workload_config(args, prec):
 # clocks sampling
 # ---------------------------------------------------------------------------------------------------
 class ClockSampler:
-    # power.draw is a ~1 s average and under-reads a sub-second timed region (it showed 550-620 W where the board sat at its
-    # 1000 W limit: scripts/power_probe.sh); power.draw.instant, the last column, is what the power fields are taken from
+    # power.draw is a ~1 s average and under-reads a sub-second timed region (it shows 550-620 W where the board sits at its
+    # 1000 W limit: scripts/power_probe.sh, profiles/r02x_power_probe.txt); it is still what selects the samples "under
+    # load" (it ramps smoothly).  power.draw.instant, the last column, is reported beside it (spiky: 1000-1200 W peaks).
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,"
          "power.draw.instant")
@@ -211,7 +212,7 @@ class ClockSampler:
         try:
             self.f = open(self.path, "w")
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+                                          "-lms", "20"], stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             self.proc = None
 
@@ -224,7 +225,7 @@ class ClockSampler:
         except subprocess.TimeoutExpired:
             self.proc.kill()
         self.f.close()
-        sm, mx, reasons, pw = [], None, set(), []
+        sm, mx, reasons, pw, pwi = [], None, set(), [], []
         with open(self.path) as f:
             for line in f:
                 parts = [x.strip() for x in line.split(",")]
@@ -237,7 +238,7 @@ class ClockSampler:
                 except ValueError:
                     continue
                 try:
-                    pw[-1] = float(parts[9])
+                    pwi.append(float(parts[9]))
                 except (ValueError, IndexError):
                     pass
                 for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[5:9]):
@@ -252,9 +253,11 @@ class ClockSampler:
         # "under load" = samples with power in the upper half of what was seen
         thr = 0.5 * (max(pw) + min(pw))
         load = [s for s, p in zip(sm, pw) if p >= thr] or sm
-        pw_load = [p for p in pw if p >= thr] or pw
-        return {"sm_mhz": statistics.median(load), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm),
-                "power_w_max": max(pw), "power_w": statistics.median(pw_load)}
+        res = {"sm_mhz": statistics.median(load), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm),
+               "power_w_max": max(pw)}
+        if pwi:
+            res["power_w_instant_max"] = max(pwi)
+        return res
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -420,9 +423,6 @@ def run_b200(args):
     launches = capi.launch_count() - launches0
     clocks = sampler.stop() if rank == 0 else None
     ms_per_step = ms_total / args.steps
-    if clocks and clocks.get("power_w"):
-        # board power under load x step time: under a board power cap the step is energy-limited
-        clocks["energy_j_per_step"] = clocks["power_w"] * ms_per_step * 1e-3
     value = world * t.n_total * args.steps / (ms_total * 1e-3)
     prof = kernel_profile(ctx, t.step, args.steps)
     final_loss = float(t.fp.loss_slot[1].item())

@@ -160,8 +160,8 @@ def test_gradient_allreduce_gloo_world2(tmp_path):
 
 def test_bench_reads_committed_traffic_table_and_parses_power_samples(tmp_path):
     """bench.py's roofline.traffic comes from the newest committed ncu capture (no constants in bench.py), and the clocks
-    block is computed from nvidia-smi samples: under-load median clock, throttle reasons, board power, for the energy
-    per step."""
+    block is computed from nvidia-smi samples: under-load median clock, throttle reasons, averaged and instantaneous board
+    power."""
     import importlib.util
     import os
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -177,7 +177,7 @@ def test_bench_reads_committed_traffic_table_and_parses_power_samples(tmp_path):
     with open(s.path, "w") as f:
         f.write("0, 1965, 1965, 180.0, 0x0, Not Active, Not Active, Not Active, Not Active, 185.0\n")
         f.write("0, 1620, 1965, 590.0, 0x4, Not Active, Not Active, Not Active, Active, 980.0\n")
-        f.write("0, 1590, 1965, 600.0, 0x4, Not Active, Not Active, Not Active, Active, [N/A]\n")   # falls back to power.draw
+        f.write("0, 1590, 1965, 600.0, 0x4, Not Active, Not Active, Not Active, Active, [N/A]\n")   # no instantaneous reading in this sample
         f.write("garbage line\n")
 
     class _P:
@@ -187,4 +187,4 @@ def test_bench_reads_committed_traffic_table_and_parses_power_samples(tmp_path):
     s.proc, s.f = _P(), open(os.devnull, "w")
     c = s.stop()
     assert c["sm_mhz"] == 1605.0 and c["sm_max_mhz"] == 1965.0 and c["reasons"] == ["sw_power_cap"]
-    assert c["power_w_max"] == 980.0 and c["power_w"] == 790.0 and c["samples"] == 3
+    assert c["power_w_max"] == 600.0 and c["power_w_instant_max"] == 980.0 and c["samples"] == 3
