@@ -71,18 +71,22 @@ __device__ __forceinline__ void act_adjoint_unit(float* g, const float* x) {
   if constexpr (ORDER == kOrderLapSum) {
     // summed second-order column per endpoint: L' = s' Q + s L with Q = sum_i dy_i^2 (forward: act_unit)
 #pragma unroll
+    // with dy = dx'/s and s' = 10 s t:  dy s' = t10 dx',  Q s' = (t10 / s) sum dx'^2;  the per-coordinate work is two
+    // accumulations and the derivative adjoint, the factors that do not depend on the coordinate are applied once
+    const float rt10 = r * t10 * kLapScale;   // forward: Lt' = kLapScale s' Q + s Lt
     for (int e = 0; e < (GEN ? 2 : 1); ++e) {
       const float gl = g[1 + NDER + e], lxp = x[1 + NDER + e];
-      float u = 0.f;                          // Q s'
+      const float glk = 2.0f * kLapScale * t10 * gl;
+      float q = 0.f, v = 0.f;
 #pragma unroll
       for (int i = 0; i < D; ++i) {
         const float dxp = x[1 + e * D + i], gd = g[1 + e * D + i];
-        const float d10 = dxp * t10;          // dy s'
-        u = fmaf(dxp * r, d10, u);
-        xb = fmaf(gd, d10, xb);
-        g[1 + e * D + i] = fmaf(gd, s, 2.0f * kLapScale * gl * d10);
+        q = fmaf(dxp, dxp, q);
+        v = fmaf(gd, dxp, v);
+        g[1 + e * D + i] = fmaf(dxp, glk, gd * s);
       }
-      u *= kLapScale;                           // forward: Lt' = kLapScale s' Q + s Lt
+      const float u = rt10 * q;                 // kLapScale Q s'
+      xb = fmaf(v, t10, xb);
       xb = fmaf(gl, fmaf(u, c2, t10 * (lxp - u)), xb);
       g[1 + NDER + e] = gl * s;
     }
