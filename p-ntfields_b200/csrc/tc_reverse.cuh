@@ -62,11 +62,11 @@ static __constant__ int c_rev_acc[kNumLayers] = {0, 1, 0, 1, 0, 0, 1, 0, 1, 0, 1
 template <int D, bool GEN, int ORDER>
 __device__ __forceinline__ void act_adjoint_unit(float* g, const float* x) {
   constexpr int NDER = GEN ? 2 * D : D;
-  const float t = __expf(-10.0f * x[0]);
+  const float t = ex2_approx(-14.4269504f * x[0]);      // exp(-10 a)
   const float s = 1.0f - t;
   const float r = __fdividef(1.0f, fmaxf(s, 1e-6f));
   const float t10 = 10.0f * t;
-  const float c2 = 10.0f * (1.0f - 2.0f * s);
+  const float c2 = fmaf(20.0f, t, -10.0f);               // 10 (1 - 2 s)
   float xb = g[0] * s;
   if constexpr (ORDER == kOrderLapSum) {
     // summed second-order column per endpoint: L' = s' Q + s L with Q = sum_i dy_i^2 (forward: act_unit)
